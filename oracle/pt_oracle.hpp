@@ -27,6 +27,7 @@
 #include <cmath>
 #include <cstdint>
 #include <limits>
+#include <type_traits>
 #include <vector>
 
 namespace pto {
@@ -260,20 +261,41 @@ template <class T> struct Shape {
     bool hit(const Ray<T>& ray, T t_min, T t_max, HitRecord<T>& out) const {
         return kind == SHAPE_SPHERE ? hit_sphere(ray, t_min, t_max, out) : hit_triangle(ray, t_min, t_max, out);
     }
-    // shape.rs:53-89
+    // shape.rs:53-89.  double / Counted: the reference's half-b quadratic, literally.
+    // float: the cancellation-free form of the same quadratic (Haines et al., Ray Tracing Gems ch. 7) that the
+    // device uses — the naive FP32 discriminant loses ~|oc|^2/r^2 ulps and cannot hold 1e-5 relative on t for
+    // small distant spheres.  Same roots, same near/far/range selection.
     bool hit_sphere(const Ray<T>& ray, T t_min, T t_max, HitRecord<T>& out) const {
         const Vec3<T>& center = a; T radius = b.x;
         Vec3<T> oc = ray.origin - center;
         T aa = ray.direction.dot(ray.direction);
-        T half_b = oc.dot(ray.direction);
-        T cc = oc.dot(oc) - radius * radius;
-        T disc = half_b * half_b - aa * cc;
-        if (disc < T(0)) return false;
-        T sqrtd = m_sqrt(disc);
-        T root = (-half_b - sqrtd) / aa;
-        if (root < t_min || t_max < root) {
-            root = (-half_b + sqrtd) / aa;
-            if (root < t_min || t_max < root) return false;
+        T root;
+        if constexpr (std::is_same<T, float>::value) {
+            T bp = -oc.dot(ray.direction);
+            T k = bp / aa;
+            Vec3<T> l(madd(k, ray.direction.x, oc.x), madd(k, ray.direction.y, oc.y), madd(k, ray.direction.z, oc.z));
+            T disc = radius * radius - l.dot(l);
+            if (disc < T(0)) return false;
+            T cc = oc.dot(oc) - radius * radius;
+            T q = bp + std::copysign(m_sqrt(aa * disc), bp);
+            T t_near = bp >= T(0) ? cc / q : q / aa;
+            T t_far = bp >= T(0) ? q / aa : cc / q;
+            root = t_near;
+            if (root < t_min || t_max < root) {
+                root = t_far;
+                if (root < t_min || t_max < root) return false;
+            }
+        } else {
+            T half_b = oc.dot(ray.direction);
+            T cc = oc.dot(oc) - radius * radius;
+            T disc = half_b * half_b - aa * cc;
+            if (disc < T(0)) return false;
+            T sqrtd = m_sqrt(disc);
+            root = (-half_b - sqrtd) / aa;
+            if (root < t_min || t_max < root) {
+                root = (-half_b + sqrtd) / aa;
+                if (root < t_min || t_max < root) return false;
+            }
         }
         Vec3<T> p = ray.at(root);
         Vec3<T> outward = (p - center) / radius;

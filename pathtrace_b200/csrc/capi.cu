@@ -1,0 +1,280 @@
+// capi.cu — extern "C" entry points of libpathtrace_b200.so (see include/pathtrace_b200.h).
+// Host-side glue only: argument checks, uploads, launches, downloads.  No CPU fallback of any kind.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "pt_internal.h"
+
+namespace {
+thread_local std::string g_last_error;
+
+int fail(pt_context* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->err = msg;
+    g_last_error = msg;
+    return code;
+}
+int keep(pt_context* ctx, int rc) {
+    if (rc && ctx) g_last_error = ctx->err;
+    return rc;
+}
+bool valid_params(const pt_render_params* p) { return p && p->strategy <= PT_STRATEGY_BRDF_ONLY && p->traversal <= PT_TRAVERSAL_BRUTE && p->t_min >= 0.0f; }
+bool valid_camera(const pt_camera* c) { return c && c->width >= 2 && c->height >= 2 && (uint64_t)c->width * c->height < (1ull << 31); }
+
+int ensure_frame(pt_context* ctx, size_t npix) {
+    if (npix > ctx->accum_px) {
+        if (ctx->d_accum) cudaFree(ctx->d_accum);
+        ctx->d_accum = nullptr; ctx->accum_px = 0;
+        PT_CUDA_CHECK(ctx, cudaMalloc(&ctx->d_accum, sizeof(float4) * npix));
+        ctx->accum_px = npix;
+    }
+    if (npix > ctx->out_px) {
+        if (ctx->d_radiance) cudaFree(ctx->d_radiance);
+        if (ctx->d_rgba) cudaFree(ctx->d_rgba);
+        ctx->d_radiance = nullptr; ctx->d_rgba = nullptr; ctx->out_px = 0;
+        PT_CUDA_CHECK(ctx, cudaMalloc(&ctx->d_radiance, sizeof(float) * 3 * npix));
+        PT_CUDA_CHECK(ctx, cudaMalloc(&ctx->d_rgba, 4 * npix));
+        ctx->out_px = npix;
+    }
+    return PT_OK;
+}
+int ensure_pinned(pt_context* ctx, size_t bytes) {
+    if (bytes > ctx->pinned_bytes) {
+        if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+        ctx->h_pinned = nullptr; ctx->pinned_bytes = 0;
+        PT_CUDA_CHECK(ctx, cudaMallocHost(&ctx->h_pinned, bytes));
+        ctx->pinned_bytes = bytes;
+    }
+    return PT_OK;
+}
+}  // namespace
+
+extern "C" {
+
+const char* pt_version(void) { return "pathtrace_b200 0.1 (sm_100a)"; }
+
+const char* pt_last_error(const pt_context* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+int32_t pt_context_create(int32_t device_id, pt_context** out) {
+    if (!out) return fail(nullptr, PT_ERR_INVALID, "pt_context_create: out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return fail(nullptr, PT_ERR_NO_DEVICE, std::string("no CUDA device: ") + cudaGetErrorString(e) + " (there is no CPU fallback)");
+    if (device_id < 0 || device_id >= count) return fail(nullptr, PT_ERR_INVALID, "pt_context_create: device_id out of range");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) return fail(nullptr, PT_ERR_NO_DEVICE, "cudaGetDeviceProperties failed");
+    if (prop.major != 10) return fail(nullptr, PT_ERR_NO_DEVICE, std::string("device is sm_") + std::to_string(prop.major) + std::to_string(prop.minor) + "; this library is built for sm_100a only");
+    pt_context* ctx = new (std::nothrow) pt_context();
+    if (!ctx) return fail(nullptr, PT_ERR_OOM, "out of host memory");
+    ctx->device = device_id;
+    ctx->sm_count = prop.multiProcessorCount;
+    if (cudaSetDevice(device_id) != cudaSuccess || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, PT_ERR_CUDA, "cannot create stream");
+    }
+    for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+    *out = ctx;
+    return PT_OK;
+}
+
+void pt_context_destroy(pt_context* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->pool_mem) cudaFree(ctx->pool_mem);
+    if (ctx->d_accum) cudaFree(ctx->d_accum);
+    if (ctx->d_radiance) cudaFree(ctx->d_radiance);
+    if (ctx->d_rgba) cudaFree(ctx->d_rgba);
+    if (ctx->d_counters) cudaFree(ctx->d_counters);
+    if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+void* pt_context_stream(pt_context* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+int32_t pt_context_synchronize(pt_context* ctx) {
+    if (!ctx) return PT_ERR_INVALID;
+    PT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return PT_OK;
+}
+
+int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_material* materials, uint32_t n, pt_scene** out) {
+    if (!ctx || !out || (n && (!shapes || !materials))) return fail(ctx, PT_ERR_INVALID, "pt_scene_create: null argument");
+    *out = nullptr;
+    if (n >= (1u << 30)) return fail(ctx, PT_ERR_INVALID, "pt_scene_create: too many objects");
+    for (uint32_t i = 0; i < n; ++i) {
+        if (shapes[i].kind > PT_SHAPE_TRIANGLE) return fail(ctx, PT_ERR_INVALID, "pt_scene_create: unknown shape kind at object " + std::to_string(i));
+        if (materials[i].kind > PT_MAT_OREN_NAYAR) return fail(ctx, PT_ERR_INVALID, "pt_scene_create: unknown material kind at object " + std::to_string(i));
+    }
+    cudaSetDevice(ctx->device);
+    pt_scene* sc = new (std::nothrow) pt_scene();
+    if (!sc) return fail(ctx, PT_ERR_OOM, "out of host memory");
+    sc->ctx = ctx;
+    sc->dev.n_objects = n;
+    // world.rs:214-225: lights = objects whose emission has non-zero length
+    std::vector<uint32_t> lights;
+    for (uint32_t i = 0; i < n; ++i)
+        if (materials[i].kind == PT_MAT_EMISSIVE) {
+            const float* e = materials[i].p;
+            if (std::sqrt((double)e[0] * e[0] + (double)e[1] * e[1] + (double)e[2] * e[2]) > 0.0) lights.push_back(i);
+        }
+    sc->dev.n_lights = (uint32_t)lights.size();
+    pt_shape* d_shapes = nullptr;
+    pt_material* d_mats = nullptr;
+    auto cleanup = [&](int rc) { if (d_shapes) cudaFree(d_shapes); if (d_mats) cudaFree(d_mats); if (rc) { pt_scene_destroy(sc); } return keep(ctx, rc); };
+    size_t n1 = n ? n : 1;
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_shapes, sizeof(pt_shape) * n1)) != cudaSuccess || (e = cudaMalloc(&d_mats, sizeof(pt_material) * n1)) != cudaSuccess ||
+        (e = cudaMalloc(&sc->dev.light_ids, 4 * (lights.size() ? lights.size() : 1))) != cudaSuccess) {
+        ctx->err = std::string("pt_scene_create: ") + cudaGetErrorString(e);
+        return cleanup(e == cudaErrorMemoryAllocation ? PT_ERR_OOM : PT_ERR_CUDA);
+    }
+    if (n) {
+        cudaMemcpyAsync(d_shapes, shapes, sizeof(pt_shape) * n, cudaMemcpyHostToDevice, ctx->stream);
+        cudaMemcpyAsync(d_mats, materials, sizeof(pt_material) * n, cudaMemcpyHostToDevice, ctx->stream);
+    }
+    if (!lights.empty()) cudaMemcpyAsync(sc->dev.light_ids, lights.data(), 4 * lights.size(), cudaMemcpyHostToDevice, ctx->stream);
+    int rc = scene_pack_launch(ctx, d_shapes, d_mats, n, sc->dev);
+    if (rc) return cleanup(rc);
+    rc = lbvh_build_device(ctx, d_shapes, n, sc->dev, nullptr);   // synchronises the stream
+    if (rc) return cleanup(rc);
+    cleanup(0);
+    *out = sc;
+    return PT_OK;
+}
+
+void pt_scene_destroy(pt_scene* sc) {
+    if (!sc) return;
+    if (sc->ctx) cudaSetDevice(sc->ctx->device);
+    void* ptrs[] = {sc->dev.prims, sc->dev.mats, sc->dev.light_ids, sc->dev.nodes, sc->dev.codes_sorted, sc->dev.prim_sorted};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    delete sc;
+}
+
+uint32_t pt_scene_num_objects(const pt_scene* s) { return s ? s->dev.n_objects : 0; }
+uint32_t pt_scene_num_lights(const pt_scene* s) { return s ? s->dev.n_lights : 0; }
+
+int32_t pt_render_accumulate_device(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, void* d_accum,
+                                    pt_stats* stats) {
+    if (!ctx || !scene || !d_accum) return fail(ctx, PT_ERR_INVALID, "pt_render_accumulate_device: null argument");
+    if (!valid_camera(cam)) return fail(ctx, PT_ERR_INVALID, "pt_render: bad camera (width/height must be >= 2)");
+    if (!valid_params(p)) return fail(ctx, PT_ERR_INVALID, "pt_render: bad render params");
+    if (scene->ctx != ctx) return fail(ctx, PT_ERR_INVALID, "pt_render: scene belongs to another context");
+    cudaSetDevice(ctx->device);
+    if (stats) std::memset(stats, 0, sizeof(*stats));
+    RenderLaunch rl{&scene->dev, *cam, *p, static_cast<float4*>(d_accum)};
+    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+    int rc = wavefront_render(ctx, rl, stats);
+    if (rc) return keep(ctx, rc);
+    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaEventSynchronize(ctx->ev[1]));
+    if (stats) { cudaEventElapsedTime(&stats->ms_render, ctx->ev[0], ctx->ev[1]); stats->ms_total = stats->ms_render; }
+    return PT_OK;
+}
+
+int32_t pt_resolve_device(pt_context* ctx, const void* d_accum, uint32_t w, uint32_t h, uint32_t total_spp, void* d_rad, void* d_rgba) {
+    if (!ctx || !d_accum || !total_spp || !w || !h) return fail(ctx, PT_ERR_INVALID, "pt_resolve_device: bad argument");
+    cudaSetDevice(ctx->device);
+    return keep(ctx, resolve_launch(ctx, static_cast<const float4*>(d_accum), w, h, total_spp, static_cast<float*>(d_rad), static_cast<uint8_t*>(d_rgba)));
+}
+
+int32_t pt_render(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, float* radiance, uint8_t* rgba,
+                  pt_stats* stats) {
+    if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_render: null argument");
+    if (!valid_camera(cam)) return fail(ctx, PT_ERR_INVALID, "pt_render: bad camera (width/height must be >= 2)");
+    if (!valid_params(p) || p->spp == 0) return fail(ctx, PT_ERR_INVALID, "pt_render: bad render params (spp must be > 0)");
+    cudaSetDevice(ctx->device);
+    size_t npix = (size_t)cam->width * cam->height;
+    int rc = ensure_frame(ctx, npix);
+    if (rc) return keep(ctx, rc);
+    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_accum, 0, sizeof(float4) * npix, ctx->stream));
+    pt_stats local;
+    rc = pt_render_accumulate_device(ctx, scene, cam, p, ctx->d_accum, &local);
+    if (rc) return rc;
+    rc = resolve_launch(ctx, ctx->d_accum, cam->width, cam->height, p->spp, radiance ? ctx->d_radiance : nullptr, rgba ? ctx->d_rgba : nullptr);
+    if (rc) return keep(ctx, rc);
+    local.kernel_launches += 1;
+    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (radiance) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(radiance, ctx->d_radiance, sizeof(float) * 3 * npix, cudaMemcpyDeviceToHost, ctx->stream));
+    if (rgba) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(rgba, ctx->d_rgba, 4 * npix, cudaMemcpyDeviceToHost, ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        *stats = local;
+        cudaEventElapsedTime(&stats->ms_total, ctx->ev[2], ctx->ev[1]);
+        cudaEventElapsedTime(&stats->ms_download, ctx->ev[3], ctx->ev[1]);
+    }
+    return PT_OK;
+}
+
+int32_t pt_trace_primary(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, int32_t jitter, float ox,
+                         float oy, uint32_t sample, int32_t* obj_id, float* t, float* dir) {
+    if (!ctx || !scene || !obj_id || !t) return fail(ctx, PT_ERR_INVALID, "pt_trace_primary: null argument");
+    if (!valid_camera(cam) || !valid_params(p)) return fail(ctx, PT_ERR_INVALID, "pt_trace_primary: bad camera or params");
+    cudaSetDevice(ctx->device);
+    size_t npix = (size_t)cam->width * cam->height;
+    int32_t* d_obj = nullptr; float *d_t = nullptr, *d_dir = nullptr;
+    PT_CUDA_CHECK(ctx, cudaMalloc(&d_obj, 4 * npix));
+    PT_CUDA_CHECK(ctx, cudaMalloc(&d_t, 4 * npix));
+    if (dir) PT_CUDA_CHECK(ctx, cudaMalloc(&d_dir, 12 * npix));
+    int rc = wavefront_trace_primary(ctx, scene->dev, *cam, *p, jitter, ox, oy, sample, d_obj, d_t, d_dir, nullptr);
+    if (!rc) {
+        cudaMemcpyAsync(obj_id, d_obj, 4 * npix, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaMemcpyAsync(t, d_t, 4 * npix, cudaMemcpyDeviceToHost, ctx->stream);
+        if (dir) cudaMemcpyAsync(dir, d_dir, 12 * npix, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) { ctx->err = std::string("pt_trace_primary: ") + cudaGetErrorString(e); rc = PT_ERR_CUDA; }
+    }
+    cudaFree(d_obj); cudaFree(d_t); if (d_dir) cudaFree(d_dir);
+    return keep(ctx, rc);
+}
+
+int32_t pt_bvh_download(pt_context* ctx, const pt_scene* scene, uint32_t* codes, uint32_t* prims, uint32_t* nodes, float* bounds) {
+    if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_bvh_download: null argument");
+    cudaSetDevice(ctx->device);
+    const SceneDev& d = scene->dev;
+    if (codes && d.n_objects) PT_CUDA_CHECK(ctx, cudaMemcpy(codes, d.codes_sorted, 4 * (size_t)d.n_objects, cudaMemcpyDeviceToHost));
+    if (prims && d.n_objects) PT_CUDA_CHECK(ctx, cudaMemcpy(prims, d.prim_sorted, 4 * (size_t)d.n_objects, cudaMemcpyDeviceToHost));
+    if (nodes) PT_CUDA_CHECK(ctx, cudaMemcpy(nodes, d.nodes, 64 * (size_t)d.n_nodes, cudaMemcpyDeviceToHost));
+    if (bounds) std::memcpy(bounds, d.bounds, 24);
+    return PT_OK;
+}
+
+// world.rs:344-369
+int32_t pt_export_luminance(const char* path, const float* rad, uint32_t W, uint32_t H) {
+    if (!path || !rad) return fail(nullptr, PT_ERR_INVALID, "pt_export_luminance: null argument");
+    FILE* f = std::fopen(path, "w");
+    if (!f) return fail(nullptr, PT_ERR_INVALID, std::string("pt_export_luminance: cannot open ") + path);
+    std::fprintf(f, "x,y,r,g,b,luminance\n");
+    for (uint32_t y = 0; y < H; ++y)
+        for (uint32_t x = 0; x < W; ++x) {
+            const float* v = rad + 3 * ((size_t)y * W + x);
+            double r = v[0], g = v[1], b = v[2];
+            double lum = 0.2126 * r + 0.7152 * g + 0.0722 * b;
+            std::fprintf(f, "%u,%u,%.6f,%.6f,%.6f,%.6f\n", x, y, r, g, b, lum);
+        }
+    std::fclose(f);
+    return PT_OK;
+}
+
+int32_t pt_write_ppm(const char* path, const uint8_t* rgba, uint32_t W, uint32_t H) {
+    if (!path || !rgba) return fail(nullptr, PT_ERR_INVALID, "pt_write_ppm: null argument");
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(nullptr, PT_ERR_INVALID, std::string("pt_write_ppm: cannot open ") + path);
+    std::fprintf(f, "P6\n%u %u\n255\n", W, H);
+    std::vector<uint8_t> row(3 * (size_t)W);
+    for (uint32_t y = 0; y < H; ++y) {
+        for (uint32_t x = 0; x < W; ++x) for (int c = 0; c < 3; ++c) row[3 * x + c] = rgba[4 * ((size_t)y * W + x) + c];
+        std::fwrite(row.data(), 1, row.size(), f);
+    }
+    std::fclose(f);
+    return PT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// pt_internal.h — host/device structs shared by the .cu files of libpathtrace_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/pathtrace_b200.h"
+
+// Scene resident in HBM (replicated per GPU).  All arrays are float4-packed for 128-bit loads.
+struct SceneDev {
+    uint32_t n_objects = 0, n_lights = 0, n_nodes = 0;
+    float4* prims = nullptr;      // 4 x float4 per object (64 B): see pt_math.cuh
+    float4* mats = nullptr;       // 2 x float4 per object (32 B): see pt_shade.cuh
+    uint32_t* light_ids = nullptr;
+    float4* nodes = nullptr;      // 4 x float4 per LBVH node (64 B): [Llo,left][Lhi,right][Rlo,0][Rhi,0]
+    uint32_t* codes_sorted = nullptr;
+    uint32_t* prim_sorted = nullptr;
+    float bounds[6] = {0, 0, 0, 0, 0, 0};
+};
+
+struct pt_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    int sm_count = 0;
+    std::string err;
+    // wavefront pool (grown on demand, reused across calls)
+    uint32_t pool_cap = 0;
+    void* pool_mem = nullptr;
+    size_t pool_bytes = 0;
+    // frame buffers owned by the context for pt_render (grown on demand)
+    float4* d_accum = nullptr; size_t accum_px = 0;
+    float* d_radiance = nullptr; uint8_t* d_rgba = nullptr; size_t out_px = 0;
+    void* h_pinned = nullptr; size_t pinned_bytes = 0;
+    uint64_t* d_counters = nullptr;   // device counters block
+    uint64_t* h_counters = nullptr;   // pinned mirror
+};
+
+struct pt_scene {
+    pt_context* ctx = nullptr;
+    SceneDev dev;
+};
+
+// lbvh.cu
+int lbvh_build_device(pt_context* ctx, const pt_shape* d_shapes, uint32_t n, SceneDev& out, uint64_t* launches);
+// wavefront.cu
+struct RenderLaunch {
+    const SceneDev* scene;
+    pt_camera cam;
+    pt_render_params prm;
+    float4* d_accum;
+};
+int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats);
+int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
+                            float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches);
+int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba);
+int scene_pack_launch(pt_context* ctx, const pt_shape* d_shapes, const pt_material* d_mats, uint32_t n, SceneDev& out);
+
+#define PT_CUDA_CHECK(ctx, expr)                                                                          \
+    do {                                                                                                  \
+        cudaError_t _e = (expr);                                                                          \
+        if (_e != cudaSuccess) {                                                                          \
+            (ctx)->err = std::string(#expr) + ": " + cudaGetErrorString(_e);                              \
+            return _e == cudaErrorMemoryAllocation ? PT_ERR_OOM : PT_ERR_CUDA;                            \
+        }                                                                                                 \
+    } while (0)

@@ -1,0 +1,612 @@
+// wavefront.cu — the Monte Carlo sample loop of roxas1533/pathtrace as sm_100a wavefront kernels.
+//
+// Replaces src/main.rs:43-60 (pixel loop) + src/world.rs:293-333 (spp loop) + src/rendering.rs:34-142
+// (MisStrategy::ray_color) / :213-265 (BrdfOnlyStrategy) with the iterative form of SURVEY Appendix A.6:
+//
+//   K1 k_generate        camera rays for a pool of P path slots            camera.rs:139-147, world.rs:297-299
+//   K3 k_trace_closest   closest hit (LBVH or brute force, smem-staged)    world.rs:270-290, shape.rs:53-89/:161-198
+//   K4/K6/K7 k_shade     emission / look-ahead MIS resolve, NEE setup, BSDF sample, Russian roulette,
+//                        shadow-queue compaction, per-pixel accumulate, in-place path regeneration
+//   K5 k_trace_shadow    any-hit over the compacted shadow queue           rendering.rs:62-65
+//   K8 k_resolve         mean, sqrt gamma, clamp, RGBA8                    world.rs:315-332
+//
+// Path state lives in HBM as SoA float4 / uint4 arrays indexed by slot; a slot whose path ends is
+// re-seeded in place with the next (pixel, sample) so the pool stays full until the work runs out.
+#include <cfloat>
+#include <cstdio>
+#include <vector>
+
+#include "pt_internal.h"
+#include "pt_shade.cuh"
+
+using namespace ptd;
+
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int kItersPerBatch = 16;
+constexpr int kStackDepth = 64;
+constexpr uint32_t kMaxSmemPrims = 1024;   // scene staged in shared memory up to this many objects
+
+// device counter block (uint64 words)
+enum { C_WORK_NEXT = 0, C_SHADOW_BASE = 1, C_ALIVE_BASE = C_SHADOW_BASE + kItersPerBatch, C_TOTAL = C_ALIVE_BASE + kItersPerBatch };
+
+struct Pool {
+    uint32_t P;
+    float4* ray_o;    // origin.xyz, eta_ratio carried by the ray (camera.rs:6)
+    float4* ray_d;    // direction.xyz, bsdf pdf of the scatter that produced the ray (MIS at look-ahead)
+    uint2* hit;       // t bits, object id (0xffffffff = miss)
+    float4* beta;     // path throughput rgb
+    float4* L;        // radiance gathered by this sample so far
+    uint4* meta;      // pixel, sample, depth, alive
+    float4* sh_o;     // shadow queue: origin.xyz, t_max
+    float4* sh_d;     // direction.xyz, slot bits
+    float4* sh_c;     // contribution if unoccluded
+    uint4* block_stats;   // per-CTA: primary, shadow, scattered, vertices (no atomics)
+};
+
+struct Frame {
+    CameraDev cam;
+    uint32_t npix;
+    uint64_t total_work;     // npix * spp of this call
+    uint32_t sample_offset, min_depth, max_depth, strategy;
+    uint32_t k0, k1;         // Philox key
+    float t_min;
+    float4* accum;           // per pixel: sum r, g, b, sum luminance^2
+};
+
+struct SceneView {
+    const float4* prims;
+    const float4* mats;
+    const uint32_t* light_ids;
+    const float4* nodes;
+    uint32_t n_objects, n_lights, n_nodes;
+};
+
+PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint4& meta) {
+    uint32_t sample = f.sample_offset + (uint32_t)(w / f.npix);
+    uint32_t pixel = (uint32_t)(w % f.npix);
+    uint32_t x = pixel % f.cam.width, y = pixel / f.cam.width;
+    uint4 r = philox4x32_10(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, u01(r.x), u01(r.y));   // world.rs:299
+    ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
+    rd = make_float4(d.x, d.y, d.z, 0.0f);
+    meta = make_uint4(pixel, sample, 0u, 1u);
+}
+
+// K1 — initial fill of the pool
+__global__ void __launch_bounds__(kBlock) k_generate(Pool pool, const __grid_constant__ Frame f, uint64_t work_base) {
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= pool.P) return;
+    uint64_t w = work_base + i;
+    if (w < f.total_work) {
+        float4 ro, rd; uint4 m;
+        make_primary(f, w, ro, rd, m);
+        pool.ray_o[i] = ro; pool.ray_d[i] = rd; pool.meta[i] = m;
+        pool.beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+        pool.L[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+        pool.meta[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
+// ------------------------------------------------------------------------------------ traversal
+// Scene staged in shared memory: [nodes: 4 float4 each][prims: 3 float4 each (q0,q1,q2)]
+template <bool SMEM>
+struct Geo {
+    const float4* nodes;
+    const float4* prims;   // stride 3 (smem) or 4 (global)
+    PT_DEV void node(int i, float4& a, float4& b, float4& c, float4& d) const {
+        if (SMEM) { a = nodes[4 * i]; b = nodes[4 * i + 1]; c = nodes[4 * i + 2]; d = nodes[4 * i + 3]; }
+        else { a = __ldg(nodes + 4 * i); b = __ldg(nodes + 4 * i + 1); c = __ldg(nodes + 4 * i + 2); d = __ldg(nodes + 4 * i + 3); }
+    }
+    PT_DEV void prim(int i, float4& q0, float4& q1, float4& q2) const {
+        if (SMEM) { q0 = prims[3 * i]; q1 = prims[3 * i + 1]; q2 = prims[3 * i + 2]; }
+        else { q0 = __ldg(prims + 4 * (size_t)i); q1 = __ldg(prims + 4 * (size_t)i + 1); q2 = __ldg(prims + 4 * (size_t)i + 2); }
+    }
+};
+template <bool SMEM>
+PT_DEV Geo<SMEM> stage_scene(const SceneView& s, float4* smem, bool want_nodes) {
+    Geo<SMEM> g;
+    if (SMEM) {
+        uint32_t nn = want_nodes ? s.n_nodes * 4 : 0;
+        for (uint32_t i = threadIdx.x; i < nn; i += blockDim.x) smem[i] = __ldg(s.nodes + i);
+        for (uint32_t i = threadIdx.x; i < s.n_objects * 3; i += blockDim.x) smem[nn + i] = __ldg(s.prims + 4 * (i / 3) + (i % 3));
+        __syncthreads();
+        g.nodes = smem; g.prims = smem + nn;
+    } else {
+        g.nodes = s.nodes; g.prims = s.prims;
+    }
+    return g;
+}
+
+// Slab test against [lo,hi]; conservative: NaN slabs (0 * inf) are ignored, far side widened by 2 ulp.
+PT_DEV bool slab(float3 lo, float3 hi, float3 ro, float3 inv, float t_min, float t_max, float& tnear) {
+    float tx0 = (lo.x - ro.x) * inv.x, tx1 = (hi.x - ro.x) * inv.x;
+    float ty0 = (lo.y - ro.y) * inv.y, ty1 = (hi.y - ro.y) * inv.y;
+    float tz0 = (lo.z - ro.z) * inv.z, tz1 = (hi.z - ro.z) * inv.z;
+    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), t_min));
+    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), t_max));
+    tnear = tn;
+    return tn <= tf * 1.0000004f;
+}
+
+// Closest hit.  Winner = smallest t in [t_min, inf); equal t -> higher object index (world.rs:281-287 scans
+// in index order with an inclusive t_max, so a later object replaces an earlier one on a tie).
+template <bool SMEM, bool BRUTE>
+PT_DEV void closest_hit(const Geo<SMEM>& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
+    best_t = FLT_MAX; best_id = -1;
+    float tmax = __int_as_float(0x7f800000);
+    auto test = [&](int id) {
+        float4 q0, q1, q2;
+        g.prim(id, q0, q1, q2);
+        float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
+        if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
+    };
+    if (BRUTE) {
+        for (int id = 0; id < (int)n_objects; ++id) test(id);
+    } else {
+        float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
+        int stack[kStackDepth];
+        int sp = 0, node = 0;
+        while (true) {
+            float4 a, b, c, d;
+            g.node(node, a, b, c, d);
+            int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
+            float tl, tr;
+            bool hl = slab(v3(a), v3(b), ro, inv, t_min, tmax, tl);
+            bool hr = slab(v3(c), v3(d), ro, inv, t_min, tmax, tr);
+            if (hl && cl < 0) { test(~cl); hl = false; }
+            if (hr && cr < 0) { test(~cr); hr = false; }
+            if (hl && hr) {
+                if (tr < tl) { int t = cl; cl = cr; cr = t; }
+                stack[sp++] = cr; node = cl;
+            } else if (hl) node = cl;
+            else if (hr) node = cr;
+            else { if (sp == 0) break; node = stack[--sp]; }
+        }
+    }
+    if (best_id >= 0) best_t = tmax;
+}
+// Any hit in [t_min, t_max] (rendering.rs:62-65)
+template <bool SMEM, bool BRUTE>
+PT_DEV bool any_hit(const Geo<SMEM>& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float t_max) {
+    if (BRUTE) {
+        bool occluded = false;
+        for (int id = 0; id < (int)n_objects; ++id) {
+            float4 q0, q1, q2;
+            g.prim(id, q0, q1, q2);
+            occluded |= hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f;
+        }
+        return occluded;
+    }
+    float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
+    int stack[kStackDepth];
+    int sp = 0, node = 0;
+    while (true) {
+        float4 a, b, c, d;
+        g.node(node, a, b, c, d);
+        int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
+        float tl, tr;
+        bool hl = slab(v3(a), v3(b), ro, inv, t_min, t_max, tl);
+        bool hr = slab(v3(c), v3(d), ro, inv, t_min, t_max, tr);
+        if (hl && cl < 0) {
+            float4 q0, q1, q2; g.prim(~cl, q0, q1, q2);
+            if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
+            hl = false;
+        }
+        if (hr && cr < 0) {
+            float4 q0, q1, q2; g.prim(~cr, q0, q1, q2);
+            if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
+            hr = false;
+        }
+        if (hl && hr) { stack[sp++] = cr; node = cl; }
+        else if (hl) node = cl;
+        else if (hr) node = cr;
+        else { if (sp == 0) return false; node = stack[--sp]; }
+    }
+}
+
+// K3 — closest hit for every live slot
+template <bool SMEM, bool BRUTE>
+__global__ void __launch_bounds__(kBlock) k_trace_closest(Pool pool, SceneView s, float t_min) {
+    extern __shared__ float4 smem[];
+    Geo<SMEM> g = stage_scene<SMEM>(s, smem, !BRUTE);
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= pool.P) return;
+    if (pool.meta[i].w == 0u) return;
+    float4 ro = pool.ray_o[i], rd = pool.ray_d[i];
+    float t; int id;
+    closest_hit<SMEM, BRUTE>(g, s.n_objects, v3(ro), v3(rd), t_min, t, id);
+    pool.hit[i] = make_uint2(__float_as_uint(t), (uint32_t)id);
+}
+
+// K5 — any-hit over the compacted shadow queue; unoccluded entries add their contribution to the slot's L
+template <bool SMEM, bool BRUTE>
+__global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s, float t_min, const uint64_t* __restrict__ count) {
+    extern __shared__ float4 smem[];
+    uint32_t n = (uint32_t)*count;
+    if (blockIdx.x * kBlock >= n) return;
+    Geo<SMEM> g = stage_scene<SMEM>(s, smem, !BRUTE);
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= n) return;
+    float4 o = pool.sh_o[i], d = pool.sh_d[i];
+    if (!any_hit<SMEM, BRUTE>(g, s.n_objects, v3(o), v3(d), t_min, o.w)) {
+        uint32_t slot = __float_as_uint(d.w);
+        float4 c = pool.sh_c[i], L = pool.L[slot];
+        pool.L[slot] = make_float4(L.x + c.x, L.y + c.y, L.z + c.z, 0.f);
+    }
+}
+
+// ------------------------------------------------------------------------------------ shade
+// CTA-wide stream compaction of a 0/1 flag: warp ballot + popc, one shared counter per warp, ONE global
+// atomic per CTA.  Returns base (value of the global counter before this CTA's add), this thread's rank
+// among the CTA's flagged threads, and the CTA total.
+struct Compact { unsigned long long base; uint32_t rank, total; };
+PT_DEV Compact block_compact(bool flag, uint64_t* counter, uint32_t* s_warp, unsigned long long* s_base, uint32_t* s_total) {
+    uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t ballot = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s_warp[warp] = __popc(ballot);
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t c = lane < kBlock / 32 ? s_warp[lane] : 0, x = c;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane < kBlock / 32) s_warp[lane] = x - c;
+        if (lane == 31) {
+            *s_total = x;
+            *s_base = x ? atomicAdd((unsigned long long*)counter, (unsigned long long)x) : 0ull;
+        }
+    }
+    __syncthreads();
+    Compact r;
+    r.base = *s_base; r.total = *s_total;
+    r.rank = s_warp[warp] + __popc(ballot & ((1u << lane) - 1));
+    __syncthreads();
+    return r;
+}
+
+// rendering.rs:91-98
+PT_DEV float rr_prob(const Frame& f, float3 tn, uint32_t depth) {
+    if (depth < f.min_depth) return 1.0f;
+    float l = fminf(luminance(tn), 1.0f);
+    if (depth >= f.max_depth) l *= exp2f(-(float)(depth - f.min_depth));
+    return l;
+}
+
+// K4 + K6 + K7 (+ K8 accumulate, + K1 regeneration) for every live slot.
+__global__ void __launch_bounds__(kBlock) k_shade(Pool pool, SceneView s, const __grid_constant__ Frame f, uint64_t* __restrict__ counters,
+                                                  int iter_in_batch) {
+    __shared__ uint32_t s_warp[kBlock / 32];
+    __shared__ unsigned long long s_base;
+    __shared__ uint32_t s_total;
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    bool in_range = i < pool.P;
+    uint4 meta = in_range ? pool.meta[i] : make_uint4(0, 0, 0, 0);
+    const bool was_alive = meta.w != 0u;
+    bool alive = was_alive;
+    bool finished = false;           // path ended this iteration: accumulate + regenerate
+    bool emit_shadow = false;
+    float3 Lsum = v3(0.f, 0.f, 0.f);
+    float3 sh_o = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
+    float sh_tmax = 0.f;
+    uint32_t n_vertex = 0, n_scatter = 0;
+    const bool mis = f.strategy == PT_STRATEGY_MIS;
+
+    if (alive) {
+        float4 ro4 = pool.ray_o[i], rd4 = pool.ray_d[i];
+        uint2 h = pool.hit[i];
+        float3 ro = v3(ro4), rd = v3(rd4);
+        float3 beta = v3(pool.beta[i]);
+        const uint32_t depth = meta.z;
+        if (h.y == 0xffffffffu) {
+            finished = true;                                  // background is black, rendering.rs:140-141
+            Lsum = v3(pool.L[i]);
+        } else {
+            const int obj = (int)h.y;
+            const float t = __uint_as_float(h.x);
+            float4 q0 = __ldg(s.prims + 4 * (size_t)obj), q1 = __ldg(s.prims + 4 * (size_t)obj + 1);
+            float4 q2 = __ldg(s.prims + 4 * (size_t)obj + 2), q3 = __ldg(s.prims + 4 * (size_t)obj + 3);
+            Mat m = load_mat(s.mats, obj);
+            float3 p = ro + rd * t;
+            const bool is_tri = __float_as_uint(q0.w) == PT_KIND_TRIANGLE;
+            float3 n_out = is_tri ? v3(q3) : (p - v3(q0)) / q1.x;     // shape.rs:195 / :86
+            const bool front = dot(rd, n_out) < 0.0f;                 // base.rs:20
+            float3 n = front ? n_out : -n_out;
+            if (m.kind == PT_MATK_EMISSIVE && dot(m.color, m.color) > 0.0f) {
+                // rendering.rs:42-49 for a primary ray; :106-121 (look-ahead MIS) for a scattered ray
+                float3 L = v3(pool.L[i]);
+                if (depth == 0) L = m.color;
+                else if (!mis) L = L + beta * m.color;                // rendering.rs:226-228
+                else {
+                    float ps;                                         // shape pdf from the previous vertex, NOT / n_lights (Q2)
+                    if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), ro, p, ld, dd); }
+                    else ps = sphere_pdf_omega(v3(q0), q1.x, ro);
+                    float pb = rd4.w;
+                    L = L + beta * (m.color * (pb / (pb + ps)));
+                }
+                finished = true;
+                Lsum = L;
+            } else {
+                n_vertex = 1;
+                uint4 b0 = philox4x32_10(meta.x, meta.y, depth, 0u, f.k0, f.k1);
+                uint4 b1 = philox4x32_10(meta.x, meta.y, depth, 1u, f.k0, f.k1);
+                // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by K5
+                bool want_shadow = false;
+                if (mis && s.n_lights > 0) {
+                    uint32_t li = __ldg(s.light_ids + urange(b0.x, s.n_lights));
+                    float4 l0 = __ldg(s.prims + 4 * (size_t)li), l1 = __ldg(s.prims + 4 * (size_t)li + 1);
+                    float4 l2 = __ldg(s.prims + 4 * (size_t)li + 2), l3 = __ldg(s.prims + 4 * (size_t)li + 3);
+                    float3 le = v3(__ldg(s.mats + 2 * (size_t)li));
+                    float3 ldir; float dist, pdf_shape;
+                    sample_light_shape(l0, l1, l2, l3, p, u01(b0.y), u01(b0.z), ldir, dist, pdf_shape);
+                    float pl = pdf_shape / (float)s.n_lights;         // world.rs:260
+                    float cos_theta = fabsf(dot(n, ldir));            // rendering.rs:68
+                    float3 fe; float pb;
+                    bsdf_eval(m, rd, ro4.w, ldir, n, fe, pb);         // inherited eta_ratio (Q3)
+                    float w_nee = pl / (pl + pb);
+                    float3 c = beta * fe * le * (w_nee * cos_theta / pl);
+                    if (finite3(c) && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
+                        want_shadow = true;
+                        sh_o = p; sh_d = ldir; sh_c = c; sh_tmax = dist - 0.001f;   // rendering.rs:64
+                    }
+                }
+                // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
+                float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
+                float3 wo, fs; float pdf, cos_s;
+                bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.w), u01(b1.x), u01(b1.y), wo, fs, pdf, cos_s);
+                float3 tn = beta * fs * (cos_s / pdf);
+                ok = ok && finite3(tn);
+                float q = ok ? rr_prob(f, tn, depth) : 0.0f;
+                if (!ok || u01(b1.z) > q) {
+                    finished = true;                                  // D of this vertex is dropped too (Q1)
+                    Lsum = v3(pool.L[i]);
+                } else {
+                    emit_shadow = want_shadow;
+                    float3 nb = tn / q;
+                    pool.beta[i] = make_float4(nb.x, nb.y, nb.z, 0.f);
+                    pool.ray_o[i] = make_float4(p.x, p.y, p.z, eta_new);      // rendering.rs:86-87
+                    pool.ray_d[i] = make_float4(wo.x, wo.y, wo.z, pdf);
+                    meta.z = depth + 1;
+                    pool.meta[i] = meta;
+                    n_scatter = 1;
+                }
+            }
+        }
+    }
+    // ---- shadow queue compaction (ballot/popc + one atomic per CTA)
+    Compact cs = block_compact(emit_shadow, counters + C_SHADOW_BASE + iter_in_batch, s_warp, &s_base, &s_total);
+    if (emit_shadow) {
+        uint32_t sidx = (uint32_t)cs.base + cs.rank;
+        pool.sh_o[sidx] = make_float4(sh_o.x, sh_o.y, sh_o.z, sh_tmax);
+        pool.sh_d[sidx] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(i));
+        pool.sh_c[sidx] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
+    }
+    // ---- K8 accumulate (world.rs:296-313: color_temp += ray_color)
+    if (finished) {
+        float lum = luminance(Lsum);
+        atomicAdd(f.accum + meta.x, make_float4(Lsum.x, Lsum.y, Lsum.z, lum * lum));
+    }
+    // ---- regeneration: finished slots take the next (pixel, sample) from the global work counter
+    Compact cw = block_compact(finished, counters + C_WORK_NEXT, s_warp, &s_base, &s_total);
+    uint32_t n_primary = 0;
+    if (finished) {
+        uint64_t w = cw.base + cw.rank;
+        if (w < f.total_work) {
+            float4 ro, rd; uint4 m;
+            make_primary(f, w, ro, rd, m);
+            pool.ray_o[i] = ro; pool.ray_d[i] = rd; pool.meta[i] = m;
+            pool.beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+            pool.L[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            n_primary = 1;
+        } else {
+            alive = false;
+            pool.meta[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
+    // ---- bookkeeping: live-slot count (one atomic per CTA) and per-CTA ray statistics (no atomics)
+    uint32_t b_alive = __syncthreads_count(alive);
+    uint32_t b_vertex = __syncthreads_count(n_vertex);
+    uint32_t b_scatter = __syncthreads_count(n_scatter);
+    uint32_t b_primary = __syncthreads_count(n_primary);
+    if (threadIdx.x == 0) {
+        if (b_alive) atomicAdd((unsigned long long*)(counters + C_ALIVE_BASE + iter_in_batch), (unsigned long long)b_alive);
+        uint4 st = pool.block_stats[blockIdx.x];
+        st.x += b_primary; st.y += cs.total; st.z += b_scatter; st.w += b_vertex;
+        pool.block_stats[blockIdx.x] = st;
+    }
+}
+
+// K8 — world.rs:315-332: mean, store linear radiance, sqrt gamma, clamp [0,1], *255 truncated, alpha 255
+__global__ void k_resolve(const float4* __restrict__ accum, uint32_t npix, float inv_spp, float* __restrict__ radiance,
+                          uchar4* __restrict__ rgba) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    float4 a = accum[i];
+    float r = a.x * inv_spp, g = a.y * inv_spp, b = a.z * inv_spp;
+    if (radiance) { radiance[3 * (size_t)i] = r; radiance[3 * (size_t)i + 1] = g; radiance[3 * (size_t)i + 2] = b; }
+    if (rgba) {
+        auto to8 = [](float v) -> unsigned char {
+            float s = sqrtf(v);
+            if (!(s == s)) return 0;   // Rust: NaN as u8 == 0
+            s = fminf(fmaxf(s, 0.0f), 1.0f);
+            return (unsigned char)(s * 255.0f);
+        };
+        rgba[i] = make_uchar4(to8(r), to8(g), to8(b), 255);
+    }
+}
+
+// Parity hook: one primary ray per pixel, closest hit only (K1 + K3 without the pool)
+template <bool SMEM, bool BRUTE>
+__global__ void __launch_bounds__(kBlock) k_trace_primary(SceneView s, const __grid_constant__ Frame f, int jitter, float ox, float oy,
+                                                          uint32_t sample, int32_t* __restrict__ obj, float* __restrict__ tt,
+                                                          float* __restrict__ dirs) {
+    extern __shared__ float4 smem[];
+    Geo<SMEM> g = stage_scene<SMEM>(s, smem, !BRUTE);
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.npix) return;
+    uint32_t x = i % f.cam.width, y = i / f.cam.width;
+    if (jitter) {
+        uint4 r = philox4x32_10(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+        ox = u01(r.x); oy = u01(r.y);
+    }
+    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
+    float t; int id;
+    closest_hit<SMEM, BRUTE>(g, s.n_objects, f.cam.origin, d, f.t_min, t, id);
+    obj[i] = id;
+    tt[i] = id >= 0 ? t : __int_as_float(0x7f800000);
+    if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
+}
+
+SceneView make_view(const SceneDev& d) {
+    SceneView v;
+    v.prims = d.prims; v.mats = d.mats; v.light_ids = d.light_ids; v.nodes = d.nodes;
+    v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
+    return v;
+}
+Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {
+    Frame f;
+    f.cam.origin = make_float3(c.origin[0], c.origin[1], c.origin[2]);
+    f.cam.llc = make_float3(c.lower_left_corner[0], c.lower_left_corner[1], c.lower_left_corner[2]);
+    f.cam.horizontal = make_float3(c.horizontal[0], c.horizontal[1], c.horizontal[2]);
+    f.cam.vertical = make_float3(c.vertical[0], c.vertical[1], c.vertical[2]);
+    f.cam.width = c.width; f.cam.height = c.height;
+    f.npix = c.width * c.height;
+    f.total_work = (uint64_t)f.npix * p.spp;
+    f.sample_offset = p.sample_offset; f.min_depth = p.min_depth; f.max_depth = p.max_depth; f.strategy = p.strategy;
+    f.k0 = (uint32_t)p.seed; f.k1 = (uint32_t)(p.seed >> 32);
+    f.t_min = p.t_min;
+    f.accum = accum;
+    return f;
+}
+struct Mode { bool smem, brute; size_t smem_bytes; };
+Mode pick_mode(const SceneDev& s, uint32_t traversal) {
+    Mode m;
+    m.brute = traversal == PT_TRAVERSAL_BRUTE || (traversal == PT_TRAVERSAL_AUTO && s.n_objects <= 16);
+    m.smem = s.n_objects <= kMaxSmemPrims;
+    m.smem_bytes = m.smem ? sizeof(float4) * ((m.brute ? 0 : (size_t)s.n_nodes * 4) + (size_t)s.n_objects * 3) : 0;
+    return m;
+}
+template <class K> int set_smem(pt_context* ctx, K kernel, size_t bytes) {
+    if (bytes > 48 * 1024) PT_CUDA_CHECK(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return PT_OK;
+}
+
+}  // namespace
+
+#define PT_DISPATCH(mode, CALL)                                       \
+    do {                                                              \
+        if (mode.smem && mode.brute) { CALL(true, true); }            \
+        else if (mode.smem) { CALL(true, false); }                    \
+        else if (mode.brute) { CALL(false, true); }                   \
+        else { CALL(false, false); }                                  \
+    } while (0)
+
+int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba) {
+    uint32_t npix = w * h;
+    k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_accum, npix, 1.0f / (float)spp, d_rad, reinterpret_cast<uchar4*>(d_rgba));
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    return PT_OK;
+}
+
+int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
+                            float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches) {
+    SceneView sv = make_view(scene);
+    Frame f = make_frame(cam, prm, nullptr);
+    Mode mode = pick_mode(scene, prm.traversal);
+    uint32_t grid = (f.npix + kBlock - 1) / kBlock;
+#define CALL(S, B)                                                                                                            \
+    {                                                                                                                         \
+        int rc = set_smem(ctx, k_trace_primary<S, B>, mode.smem_bytes);                                                       \
+        if (rc) return rc;                                                                                                    \
+        k_trace_primary<S, B><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir); \
+    }
+    PT_DISPATCH(mode, CALL);
+#undef CALL
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    if (launches) *launches += 1;
+    return PT_OK;
+}
+
+static int ensure_pool(pt_context* ctx, uint32_t P, Pool& pool) {
+    uint32_t nblocks = (P + kBlock - 1) / kBlock;
+    size_t per_slot = 16 * 8 + 8 + 16;   // 8 float4 arrays + hit (uint2) + meta (uint4)
+    size_t bytes = per_slot * (size_t)P + 16 * (size_t)nblocks + 256 * 16;
+    if (bytes > ctx->pool_bytes) {
+        if (ctx->pool_mem) cudaFree(ctx->pool_mem);
+        ctx->pool_mem = nullptr; ctx->pool_bytes = 0;
+        PT_CUDA_CHECK(ctx, cudaMalloc(&ctx->pool_mem, bytes));
+        ctx->pool_bytes = bytes;
+    }
+    char* p = static_cast<char*>(ctx->pool_mem);
+    auto take = [&](size_t n) { char* r = p; p += (n + 255) & ~size_t(255); return r; };
+    pool.P = P;
+    pool.ray_o = (float4*)take(16 * (size_t)P); pool.ray_d = (float4*)take(16 * (size_t)P);
+    pool.beta = (float4*)take(16 * (size_t)P); pool.L = (float4*)take(16 * (size_t)P);
+    pool.sh_o = (float4*)take(16 * (size_t)P); pool.sh_d = (float4*)take(16 * (size_t)P); pool.sh_c = (float4*)take(16 * (size_t)P);
+    pool.meta = (uint4*)take(16 * (size_t)P);
+    pool.hit = (uint2*)take(8 * (size_t)P);
+    pool.block_stats = (uint4*)take(16 * (size_t)nblocks);
+    return PT_OK;
+}
+
+int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
+    cudaStream_t st = ctx->stream;
+    const SceneDev& scene = *rl.scene;
+    SceneView sv = make_view(scene);
+    Frame f = make_frame(rl.cam, rl.prm, rl.d_accum);
+    Mode mode = pick_mode(scene, rl.prm.traversal);
+    uint64_t launches = 0, iters = 0;
+    if (f.total_work == 0) { if (stats) { stats->samples = 0; } return PT_OK; }
+
+    uint32_t P = rl.prm.path_pool ? rl.prm.path_pool : (1u << 20);
+    if ((uint64_t)P > f.total_work) P = (uint32_t)f.total_work;
+    P = (P + kBlock - 1) / kBlock * kBlock;
+    Pool pool;
+    int rc = ensure_pool(ctx, P, pool);
+    if (rc) return rc;
+    uint32_t grid = P / kBlock;
+    if (!ctx->d_counters) {
+        PT_CUDA_CHECK(ctx, cudaMalloc(&ctx->d_counters, 8 * C_TOTAL));
+        PT_CUDA_CHECK(ctx, cudaMallocHost(&ctx->h_counters, 8 * C_TOTAL));
+    }
+#define SETS(S, B) { rc = set_smem(ctx, k_trace_closest<S, B>, mode.smem_bytes); if (rc) return rc; rc = set_smem(ctx, k_trace_shadow<S, B>, mode.smem_bytes); if (rc) return rc; }
+    PT_DISPATCH(mode, SETS);
+#undef SETS
+    uint64_t first = (uint64_t)P < f.total_work ? (uint64_t)P : f.total_work;
+    PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_counters + C_WORK_NEXT, &first, 8, cudaMemcpyHostToDevice, st));
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(pool.block_stats, 0, 16 * (size_t)grid, st));
+    k_generate<<<grid, kBlock, 0, st>>>(pool, f, 0ull); launches++;
+    const bool mis = rl.prm.strategy == PT_STRATEGY_MIS && scene.n_lights > 0;
+    bool done = false;
+    while (!done) {
+        PT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counters + C_SHADOW_BASE, 0, 8 * (C_TOTAL - C_SHADOW_BASE), st));
+        for (int it = 0; it < kItersPerBatch; ++it) {
+#define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
+            PT_DISPATCH(mode, TRACE);
+#undef TRACE
+            k_shade<<<grid, kBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
+            launches += 2;
+            if (mis) {
+#define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, ctx->d_counters + C_SHADOW_BASE + it)
+                PT_DISPATCH(mode, SHADOW);
+#undef SHADOW
+                launches++;
+            }
+        }
+        iters += kItersPerBatch;
+        PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 8 * C_TOTAL, cudaMemcpyDeviceToHost, st));
+        PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
+        done = ctx->h_counters[C_ALIVE_BASE + kItersPerBatch - 1] == 0;
+    }
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    if (stats) {
+        std::vector<uint4> bs(grid);
+        PT_CUDA_CHECK(ctx, cudaMemcpy(bs.data(), pool.block_stats, 16 * (size_t)grid, cudaMemcpyDeviceToHost));
+        uint64_t a = 0, b = 0, c = 0, d = 0;
+        for (auto& v : bs) { a += v.x; b += v.y; c += v.z; d += v.w; }
+        stats->samples = f.total_work;
+        stats->rays_primary = a + first; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
+        stats->wavefront_iters = iters; stats->kernel_launches = launches;
+    }
+    return PT_OK;
+}
