@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native pathtrace sample loop.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched under torch.distributed.run)
+  python bench.py --impl reference --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[1]): the reference's default scene (src/world.rs:65-241) at 1920x1080,
+1024 spp, MIS, Russian roulette from depth 4, soft max depth 50.  A "step" renders that whole frame once.
+metric = Msamples/s = W*H*spp / time.  N GPUs split the samples per pixel (disjoint Philox sample indices),
+one NCCL reduce(sum) of the W*H float4 buffer to rank 0, resolve on rank 0 — total work fixed => "strong".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WIDTH, HEIGHT, SPP = 1920, 1080, 1024
+WORKLOAD = "default Cornell scene (13 objects, world.rs:65-241) 1920x1080 1024spp MIS max_depth=50"
+
+
+# ------------------------------------------------------------------------------------------------ helpers
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index=0):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); smax.append(float(r[2])); power.append(float(r[3]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "power_w_max": float(max(power)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "MEASURED_PEAKS.json"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback (B200_PROFILING.md)"
+
+
+def default_scene_arrays():
+    from pathtrace_b200 import scenes
+    return scenes.default_scene(WIDTH, HEIGHT)
+
+
+def oracle_cam(O, cam):
+    c = O.CameraDesc()
+    for name in ("origin", "lower_left_corner", "horizontal", "vertical"):
+        v = getattr(cam, name)
+        getattr(c, name)[:] = [v.x, v.y, v.z]
+    c.width, c.height = cam.width, cam.height
+    return c
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank):
+    """The reference's own CPU implementation of the path, restated (oracle/: f64, brute-force hit_scene, literal
+    recursive MIS incl. the repeated look-ahead trace, one task per pixel over all host threads).  The Rust
+    reference itself cannot be built on this image (no rustc/cargo; needs a window) — DESIGN.md."""
+    if rank != 0:
+        return
+    from oracle import pyoracle as O
+    O.build()
+    sh, mt, cam = default_scene_arrays()
+    oc = oracle_cam(O, cam)
+    spp_step = args.ref_spp
+    threads = O.lib().pto_num_threads()
+    samples = WIDTH * HEIGHT * spp_step
+    for w in range(args.warmup):
+        O.render(oc, sh, mt, O.RenderParams(spp=1, sample_offset=w), "f64", recursive=True)
+    t0 = time.perf_counter()
+    rays = 0
+    for k in range(args.steps):
+        r = O.render(oc, sh, mt, O.RenderParams(spp=spp_step, sample_offset=1000 + k * spp_step), "f64", recursive=True)
+        c = r["counters"]
+        rays += c["primary"] + c["shadow"] + c["scattered"]
+    dt = time.perf_counter() - t0
+    val = samples * args.steps / dt / 1e6
+    sample = f"{WIDTH}x{HEIGHT} at {spp_step} spp per step (of the workload's {SPP}); samples/s is spp-independent"
+    print(json.dumps({
+        "impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD, "step_sample": sample},
+        "mrays_per_s": rays / dt / 1e6,
+        "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from pathtrace_b200 import api
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+    ctx = api.Context(local_rank)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    sh, mt, cam = default_scene_arrays()
+    scene = api.Scene(ctx, sh, mt)
+    npix = WIDTH * HEIGHT
+    spp_total = args.spp
+    spp_g = spp_total // world + (1 if rank < spp_total % world else 0)
+    off_g = rank * (spp_total // world) + min(rank, spp_total % world)
+    accum = torch.zeros(npix, 4, device=dev, dtype=torch.float32)
+    radiance = torch.empty(npix, 3, device=dev, dtype=torch.float32)
+    rgba = torch.empty(npix, 4, device=dev, dtype=torch.uint8)
+    h_radiance = torch.empty(npix, 3, dtype=torch.float32).pin_memory()
+    h_rgba = torch.empty(npix, 4, dtype=torch.uint8).pin_memory()
+    flush = torch.empty(256 << 20, device=dev, dtype=torch.uint8)   # > 126 MB L2
+    params = api.render_params(spp=spp_g, sample_offset=off_g, path_pool=args.pool, profile=args.profile_in_timed)
+    totals = {"launches": 0, "rays": 0, "samples": 0, "stats": []}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step(sc):
+        """inputs resident in HBM: zero sum buffer, render this rank's spp share, reduce to rank 0, resolve."""
+        with torch.cuda.stream(ext):
+            flush.zero_()            # L2 flush between timed iterations
+            accum.zero_()
+            st = api.render_accumulate_device(ctx, sc, cam, params, accum.data_ptr())
+            if world > 1:
+                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                api.resolve_device(ctx, accum.data_ptr(), WIDTH, HEIGHT, spp_total, radiance.data_ptr(), rgba.data_ptr())
+        totals["launches"] += st["kernel_launches"] + 3 + (1 if rank == 0 else 0)
+        totals["rays"] += st["rays_primary"] + st["rays_shadow"] + st["rays_scattered"]
+        totals["samples"] += st["samples"]
+        totals["stats"].append(st)
+        return st
+
+    # ---- value: device-resident timing
+    for _ in range(args.warmup):
+        device_step(scene)
+    totals.update(launches=0, rays=0, samples=0, stats=[])
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(args.steps):
+        device_step(scene)
+    e1.record(ext)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    agg = torch.tensor([totals["launches"], totals["rays"], totals["samples"]], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+    ms_total = float(ms.item())
+    launches, rays, samples = (float(x) for x in agg.tolist())
+    value = npix * spp_total * args.steps / (ms_total * 1e-3) / 1e6
+    dev_stats = list(totals["stats"])
+
+    # ---- e2e: host buffers in, host buffers out, through the public API
+    h2d = sh.nbytes + mt.nbytes + 56 + 48
+    d2h = h_radiance.numel() * 4 + h_rgba.numel()
+
+    def e2e_step():
+        sc = api.Scene(ctx, sh, mt)               # host arrays -> HBM + LBVH build
+        if world == 1:
+            api.render(ctx, sc, cam, params)      # pt_render: host radiance + RGBA8 buffers (D2H inside)
+        else:
+            device_step(sc)
+            if rank == 0:
+                with torch.cuda.stream(ext):
+                    h_radiance.copy_(radiance, non_blocking=True)
+                    h_rgba.copy_(rgba, non_blocking=True)
+                ext.synchronize()
+        sc.close()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = npix * spp_total * args.steps / float(dt.item()) / 1e6
+
+    # ---- roofline of the dominant kernel (rank 0): per-kernel CUDA-event times + algorithmic flops from the oracle
+    roofline = roofline_hbm = cpu_baseline = None
+    kernel_ms = None
+    if rank == 0:
+        peaks, peaks_src = measured_peaks()
+        if args.profile_in_timed:
+            prof_stats = dev_stats
+        else:   # same workload, PT_FLAG_PROFILE on: events around every launch (outside the timed region)
+            pp = api.render_params(spp=spp_g, sample_offset=off_g, path_pool=args.pool, profile=True)
+            with torch.cuda.stream(ext):
+                accum.zero_()
+                prof_stats = [api.render_accumulate_device(ctx, scene, cam, pp, accum.data_ptr())]
+        kernel_ms = {k: sum(s["ms_kernel"][k] for s in prof_stats) for k in api.KERNEL_CLASSES}
+        n_kernel = {k: sum(s["n_kernel"][k] for s in prof_stats) for k in api.KERNEL_CLASSES}
+        fp32_tf, _ = api.measure_fp32_peak(ctx)
+        fp32_nominal = 148 * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+        try:
+            from oracle import pyoracle as O
+            O.build()
+            fl = O.count_flops(oracle_cam(O, cam), sh, mt, O.RenderParams(spp=1), stride=6)
+            r_closest = sum(s["rays_primary"] + s["rays_scattered"] for s in prof_stats)
+            r_shadow = sum(s["rays_shadow"] for s in prof_stats)
+            verts = sum(s["path_vertices"] for s in prof_stats)
+            flops = {"trace_closest": fl["flops_closest_per_ray"] * r_closest, "trace_shadow": fl["flops_shadow_per_ray"] * r_shadow,
+                     "shade": fl["flops_shade_per_vertex"] * verts, "generate": 0.0}
+            dom = max(kernel_ms, key=kernel_ms.get)
+            ach = flops[dom] / (kernel_ms[dom] * 1e-3) / 1e12
+            whole = fl["flops_per_sample"] * value * 1e6 / 1e12
+            roofline = {"bound": "fp32", "kernel": "k_" + dom, "achieved": ach, "peak": fp32_tf, "unit": "TFLOP/s", "frac": ach / fp32_tf,
+                        "traffic": None, "peak_source": "in-run FFMA microbenchmark (pt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
+                        "peak_nominal": fp32_nominal, "frac_of_nominal": ach / fp32_nominal,
+                        "launches": n_kernel[dom], "avg_launch_ms": kernel_ms[dom] / max(n_kernel[dom], 1),
+                        "algorithmic_flops_per_ray": fl["flops_closest_per_ray"] if dom == "trace_closest" else fl["flops_shadow_per_ray"] if dom == "trace_shadow" else fl["flops_shade_per_vertex"],
+                        "kernel_share_of_step": kernel_ms[dom] / max(sum(kernel_ms.values()), 1e-9),
+                        "whole_step": {"flops_per_sample": fl["flops_per_sample"], "achieved": whole, "frac": whole / fp32_tf},
+                        "note": "algorithmic flops counted from the reference's arithmetic by the oracle's counting scalar (FMA=2, no re-trace)"}
+            # queue traffic (implementation overhead, reported separately; never added to roofline.achieved)
+            qb = 56.0 * r_closest + 200.0 * verts + 64.0 * r_shadow
+            t_all = sum(kernel_ms.values()) * 1e-3
+            roofline_hbm = {"bound": "hbm", "what": "wavefront queue traffic (path state, hits, shadow queue)", "achieved": qb / t_all / 1e9,
+                            "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": qb / t_all / 1e9 / peaks["hbm_gbs"], "peak_source": peaks_src,
+                            "bytes_per_ray_closest": 56, "bytes_per_vertex_shade": 200, "bytes_per_shadow_ray": 64}
+            # ---- CPU baseline: the oracle (port of the reference's CPU path) on this box's host cores, bounded sample
+            if world == 1 and not args.no_cpu_baseline:
+                oc = oracle_cam(O, cam)
+                O.render(oc, sh, mt, O.RenderParams(spp=1), "f64", recursive=True)
+                r = O.render(oc, sh, mt, O.RenderParams(spp=args.cpu_spp, sample_offset=7), "f64", recursive=True)
+                cpu_baseline = {"value": npix * args.cpu_spp / r["seconds"] / 1e6, "unit": "Msamples/s", "cores": O.lib().pto_num_threads(),
+                                "kind": "port", "sample": f"{WIDTH}x{HEIGHT} at {args.cpu_spp} spp (of {SPP}); f64, brute-force scan, recursive MIS with re-trace, OpenMP dynamic per pixel",
+                                "seconds": r["seconds"]}
+        except Exception as e:   # the oracle is a checker; the bench line survives without it
+            roofline = {"bound": "fp32", "error": f"oracle unavailable: {e}", "peak": fp32_tf, "unit": "TFLOP/s"}
+
+    if rank == 0:
+        st0 = dev_stats[0]
+        line = {
+            "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "width": WIDTH, "height": HEIGHT, "spp": spp_total, "spp_per_gpu": spp_g, "strategy": "mis",
+                       "parallelism": f"spp-split x{world} + 1 NCCL reduce(sum)", "path_pool": st0["path_pool"],
+                       "l2": "explicit 256 MiB write between steps; path-state working set also exceeds L2"},
+            "mrays_per_s": rays / (ms_total * 1e-3) / 1e6, "rays_per_sample": rays / max(samples, 1),
+            "gpu_launches": int(launches), "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "what": "pt_scene_create(host arrays)+pt_render(host radiance+RGBA8 buffers)" if world == 1 else
+                            "scene upload per rank + render + NCCL reduce + resolve + D2H on rank 0"},
+            "roofline": roofline, "roofline_hbm": roofline_hbm, "kernel_ms": kernel_ms, "cpu_baseline": cpu_baseline,
+        }
+        print(json.dumps(line))
+    scene.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--spp", type=int, default=SPP)
+    ap.add_argument("--pool", type=int, default=0, help="wavefront path pool (0 = library default)")
+    ap.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU-baseline sample")
+    ap.add_argument("--ref-spp", type=int, default=2, help="spp per step of the --impl reference arm")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-in-timed", action="store_true", help="record per-kernel events inside the timed steps")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

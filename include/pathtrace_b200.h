@@ -60,7 +60,10 @@ typedef struct {
     uint64_t seed;           /* Philox key */
     float t_min;             /* 0.001 (rendering.rs:41,:64,:105) */
     uint32_t path_pool;      /* wavefront pool size in paths; 0 = default */
+    uint32_t flags;          /* PT_FLAG_* */
 } pt_render_params;
+enum { PT_FLAG_PROFILE = 1 /* time every kernel launch with CUDA events into pt_stats.ms_kernel (slower) */ };
+enum { PT_K_GENERATE = 0, PT_K_TRACE_CLOSEST = 1, PT_K_SHADE = 2, PT_K_TRACE_SHADOW = 3, PT_K_COUNT = 4 };
 
 typedef struct {
     uint64_t samples;           /* camera samples started */
@@ -70,6 +73,9 @@ typedef struct {
     uint64_t kernel_launches;   /* kernels launched by this call */
     float ms_total;             /* device time of the call, CUDA events */
     float ms_upload, ms_render, ms_download;
+    float ms_kernel[4];         /* PT_FLAG_PROFILE only: summed CUDA-event time per kernel class (PT_K_*) */
+    uint32_t n_kernel[4];       /* launches per kernel class */
+    uint32_t path_pool;         /* pool size actually used */
 } pt_stats;
 
 typedef struct pt_context pt_context;
@@ -118,6 +124,10 @@ uint32_t pt_scene_num_lights(const pt_scene* scene);
 int32_t pt_export_luminance(const char* path, const float* radiance_rgb, uint32_t width, uint32_t height);
 /* Headless stand-in for World::draw (world.rs:335-341): binary PPM (P6) of the RGBA8 buffer. */
 int32_t pt_write_ppm(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+
+/* FP32 FMA microbenchmark on this device (roofline denominator measured in the same run): dense independent
+ * FFMA chains on every SM; returns TFLOP/s counting an FMA as 2 flops. */
+int32_t pt_measure_fp32_peak(pt_context* ctx, float* tflops_out, float* ms_out);
 
 const char* pt_version(void);
 

@@ -39,8 +39,12 @@ struct Counted {
     double v;
     Counted() : v(0) {}
     Counted(double x) : v(x) {}
-    static uint64_t& flops() { static thread_local uint64_t n = 0; return n; }
+    // flop counters by category: 0 = shading / everything else, 1 = closest-hit scans, 2 = shadow scans
+    static int& cat() { static thread_local int c = 0; return c; }
+    static uint64_t* counters() { static thread_local uint64_t n[3] = {0, 0, 0}; return n; }
+    static uint64_t& flops() { return counters()[cat()]; }
 };
+struct CatScope { int prev; explicit CatScope(int c) : prev(Counted::cat()) { Counted::cat() = c; } ~CatScope() { Counted::cat() = prev; } };
 inline Counted operator+(Counted a, Counted b) { Counted::flops()++; return Counted(a.v + b.v); }
 inline Counted operator-(Counted a, Counted b) { Counted::flops()++; return Counted(a.v - b.v); }
 inline Counted operator*(Counted a, Counted b) { Counted::flops()++; return Counted(a.v * b.v); }
@@ -758,7 +762,9 @@ template <class T> struct World {
         HitRecord<T> hit; uint32_t obj = 0;
         if (rc) rc->primary++;
         if (path_len) *path_len = 0;
-        if (!hit_scene(ray, t_min, inf(), hit, obj)) return L;
+        bool hit0;
+        { CatScope cs(1); hit0 = hit_scene(ray, t_min, inf(), hit, obj); }
+        if (!hit0) return L;
         Vec3<T> le0 = materials[obj].emit();
         if (to_double(le0.length()) > 0.0) return le0;
         for (uint32_t depth = 0;; ++depth) {
@@ -773,7 +779,9 @@ template <class T> struct World {
                 Ray<T> shadow(hit.point, light_dir);
                 HitRecord<T> sh; uint32_t so = 0;
                 if (rc) rc->shadow++;
-                if (!hit_scene(shadow, t_min, distance - T(0.001), sh, so)) {
+                bool occluded;
+                { CatScope cs(2); occluded = hit_scene(shadow, t_min, distance - T(0.001), sh, so); }
+                if (!occluded) {
                     T cos_theta = m_abs(hit.normal.dot(light_dir));
                     BsdfEval<T> e = materials[obj].bsdf_pdf(ray, light_dir, hit.normal);
                     T w_nee = ls.pdf / (ls.pdf + e.pdf);
@@ -792,7 +800,9 @@ template <class T> struct World {
             scattered.eta_ratio = ray.eta_ratio;
             HitRecord<T> h2; uint32_t o2 = 0;
             if (rc) rc->scattered++;
-            if (!hit_scene(scattered, t_min, inf(), h2, o2)) return L;
+            bool hit2;
+            { CatScope cs(1); hit2 = hit_scene(scattered, t_min, inf(), h2, o2); }
+            if (!hit2) return L;
             Vec3<T> le = materials[o2].emit();
             if (to_double(le.length()) > 0.0) {
                 if (!mis) return L + beta * le;

@@ -140,13 +140,15 @@ void pto_sample(int precision, int recursive, const CameraDesc* cam, const Shape
 }
 
 // Counting-scalar run: iterative form (no redundant re-trace, Q8) over a pixel window.
-// out[0] = flops, out[1] = samples, out[2] = unique rays, out[3] = path vertices.
+// out[0] = flops, out[1] = samples, out[2] = unique rays, out[3] = path vertices,
+// out[4..6] = flops in shading / closest-hit scans / shadow scans, out[7..9] = primary / shadow / scattered rays.
 void pto_count_flops(const CameraDesc* cam, const ShapeDesc* sh, const MaterialDesc* mt, uint32_t n, const RenderParams* p,
-                     uint32_t stride, double out[4]) {
+                     uint32_t stride, double out[10]) {
     World<Counted> w(*cam, sh, mt, n, *p);
     RayCounters rc;
     uint64_t samples = 0, plen = 0;
-    Counted::flops() = 0;
+    for (int c = 0; c < 3; ++c) Counted::counters()[c] = 0;
+    Counted::cat() = 0;
     for (uint32_t y = 0; y < cam->height; y += stride)
         for (uint32_t x = 0; x < cam->width; x += stride)
             for (uint32_t sp = 0; sp < p->spp; ++sp) {
@@ -154,8 +156,11 @@ void pto_count_flops(const CameraDesc* cam, const ShapeDesc* sh, const MaterialD
                 w.sample_radiance(x, y, p->sample_offset + sp, false, &rc, &pl);
                 samples++; plen += pl;
             }
-    out[0] = (double)Counted::flops(); out[1] = (double)samples;
+    uint64_t* fc = Counted::counters();
+    out[0] = (double)(fc[0] + fc[1] + fc[2]); out[1] = (double)samples;
     out[2] = (double)(rc.primary + rc.shadow + rc.scattered); out[3] = (double)plen;
+    out[4] = (double)fc[0]; out[5] = (double)fc[1]; out[6] = (double)fc[2];
+    out[7] = (double)rc.primary; out[8] = (double)rc.shadow; out[9] = (double)rc.scattered;
 }
 
 // world.rs:315-332 on a buffer of per-pixel means (3 doubles per pixel) -> RGBA8

@@ -126,10 +126,12 @@ def sample(cam, shapes, mats, params, x, y, s, precision="f64", recursive=True):
 def count_flops(cam, shapes, mats, params, stride=1):
     """Counting-scalar run: dict(flops_per_sample, rays_per_sample, vertices_per_sample, samples)."""
     shapes, mats, n = _scene(shapes, mats)
-    out = np.zeros(4, np.float64)
+    out = np.zeros(10, np.float64)
     lib().pto_count_flops(C.byref(cam), _p(shapes), _p(mats), n, C.byref(params), C.c_uint32(stride), _p(out))
     return dict(flops_per_sample=out[0] / out[1], rays_per_sample=out[2] / out[1], vertices_per_sample=out[3] / out[1],
-                samples=int(out[1]))
+                samples=int(out[1]), flops_shade_per_vertex=out[4] / max(out[3], 1), flops_closest_per_ray=out[5] / max(out[7] + out[9], 1),
+                flops_shadow_per_ray=out[6] / max(out[8], 1), flops_shade=out[4], flops_closest=out[5], flops_shadow=out[6],
+                rays_primary=out[7], rays_shadow=out[8], rays_scattered=out[9], vertices=out[3])
 
 
 def tonemap(mean):

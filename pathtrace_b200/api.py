@@ -30,16 +30,23 @@ class pt_camera(C.Structure):
 class pt_render_params(C.Structure):
     _fields_ = [("spp", C.c_uint32), ("sample_offset", C.c_uint32), ("min_depth", C.c_uint32), ("max_depth", C.c_uint32),
                 ("strategy", C.c_uint32), ("traversal", C.c_uint32), ("seed", C.c_uint64), ("t_min", C.c_float),
-                ("path_pool", C.c_uint32)]
+                ("path_pool", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class pt_stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_scattered", C.c_uint64),
                 ("path_vertices", C.c_uint64), ("wavefront_iters", C.c_uint64), ("kernel_launches", C.c_uint64),
-                ("ms_total", C.c_float), ("ms_upload", C.c_float), ("ms_render", C.c_float), ("ms_download", C.c_float)]
+                ("ms_total", C.c_float), ("ms_upload", C.c_float), ("ms_render", C.c_float), ("ms_download", C.c_float),
+                ("ms_kernel", C.c_float * 4), ("n_kernel", C.c_uint32 * 4), ("path_pool", C.c_uint32)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        d = {k: getattr(self, k) for k, _ in self._fields_}
+        d["ms_kernel"] = dict(zip(KERNEL_CLASSES, list(self.ms_kernel)))
+        d["n_kernel"] = dict(zip(KERNEL_CLASSES, list(self.n_kernel)))
+        return d
+
+
+KERNEL_CLASSES = ("generate", "trace_closest", "shade", "trace_shadow")
 
 
 STRATEGY = {"mis": 0, "brdf_only": 1}
@@ -48,7 +55,7 @@ TRAVERSAL = {"auto": 0, "bvh": 1, "brute": 2}
 # every symbol include/pathtrace_b200.h declares
 EXPORTS = ["pt_context_create", "pt_context_destroy", "pt_last_error", "pt_scene_create", "pt_scene_destroy", "pt_render",
            "pt_render_accumulate_device", "pt_resolve_device", "pt_context_stream", "pt_context_synchronize", "pt_trace_primary",
-           "pt_bvh_download", "pt_scene_num_objects", "pt_scene_num_lights", "pt_export_luminance", "pt_write_ppm", "pt_version"]
+           "pt_bvh_download", "pt_scene_num_objects", "pt_scene_num_lights", "pt_export_luminance", "pt_write_ppm", "pt_version", "pt_measure_fp32_peak"]
 
 _lib = None
 
@@ -92,10 +99,10 @@ def camera_struct(cam: Camera) -> pt_camera:
 
 
 def render_params(spp=3000, sample_offset=0, min_depth=4, max_depth=50, strategy="mis", traversal="auto", seed=0x5EED,
-                  t_min=1e-3, path_pool=0) -> pt_render_params:
+                  t_min=1e-3, path_pool=0, profile=False) -> pt_render_params:
     s = STRATEGY[strategy] if isinstance(strategy, str) else int(strategy)
     t = TRAVERSAL[traversal] if isinstance(traversal, str) else int(traversal)
-    return pt_render_params(spp, sample_offset, min_depth, max_depth, s, t, seed, t_min, path_pool)
+    return pt_render_params(spp, sample_offset, min_depth, max_depth, s, t, seed, t_min, path_pool, 1 if profile else 0)
 
 
 class Context:
@@ -205,6 +212,13 @@ def trace_primary(ctx: Context, scene: Scene, cam: Camera, params: pt_render_par
     ctx.check(ctx.lib.pt_trace_primary(ctx.handle, scene.handle, C.byref(c), C.byref(params), C.c_int32(int(jitter)), C.c_float(ox),
                                        C.c_float(oy), C.c_uint32(sample), _ptr(ids), _ptr(t), _ptr(dirs)), "pt_trace_primary")
     return ids, t, dirs
+
+
+def measure_fp32_peak(ctx: Context):
+    """(TFLOP/s, ms) of the FFMA microbenchmark on this device."""
+    tf, ms = C.c_float(), C.c_float()
+    ctx.check(ctx.lib.pt_measure_fp32_peak(ctx.handle, C.byref(tf), C.byref(ms)), "pt_measure_fp32_peak")
+    return tf.value, ms.value
 
 
 def export_luminance(path: str, radiance: np.ndarray):

