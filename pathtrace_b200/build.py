@@ -12,7 +12,7 @@ from concurrent.futures import ThreadPoolExecutor
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIBDIR = os.path.join(_HERE, "lib")
-LIB = os.path.join(LIBDIR, "libpathtrace_b200.so")
+LIB = os.environ.get("PT_LIB") or os.path.join(LIBDIR, "libpathtrace_b200.so")   # PT_LIB: development override (kernel variants)
 SOURCES = ["capi.cu", "lbvh.cu", "wavefront.cu"]
 HEADERS = ["pt_internal.h", "pt_math.cuh", "pt_shade.cuh", os.path.join("..", "..", "include", "pathtrace_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
@@ -44,7 +44,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("PT_NVCC_EXTRA", "").split(), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -20,7 +20,9 @@ int keep(pt_context* ctx, int rc) {
     if (rc && ctx) g_last_error = ctx->err;
     return rc;
 }
-bool valid_params(const pt_render_params* p) { return p && p->strategy <= PT_STRATEGY_BRDF_ONLY && p->traversal <= PT_TRAVERSAL_BRUTE && p->t_min >= 0.0f; }
+bool valid_params(const pt_render_params* p) { return p && p->strategy <= PT_STRATEGY_BRDF_ONLY && p->traversal <= PT_TRAVERSAL_BRUTE && p->t_min >= 0.0f &&
+           (uint64_t)p->sample_offset + p->spp <= (1ull << 24);   // global sample index is packed into 24 bits of the path state
+}
 bool valid_camera(const pt_camera* c) { return c && c->width >= 2 && c->height >= 2 && (uint64_t)c->width * c->height < (1ull << 31); }
 
 int ensure_frame(pt_context* ctx, size_t npix) {

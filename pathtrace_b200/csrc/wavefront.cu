@@ -24,6 +24,13 @@ using namespace ptd;
 namespace {
 
 constexpr int kBlock = 256;
+#ifndef PT_SHADE_BLOCK
+#define PT_SHADE_BLOCK 256
+#endif
+#ifndef PT_SHADE_MIN_BLOCKS
+#define PT_SHADE_MIN_BLOCKS 3
+#endif
+constexpr int kShadeBlock = PT_SHADE_BLOCK, kShadeMinBlocks = PT_SHADE_MIN_BLOCKS;
 constexpr int kItersPerBatch = 16;
 constexpr int kStackDepth = 64;
 constexpr uint32_t kMaxSmemPrims = 1024;   // scene staged in shared memory up to this many objects
@@ -38,7 +45,7 @@ struct Pool {
     uint2* hit;       // t bits, object id (0xffffffff = miss)
     float4* beta;     // path throughput rgb
     float4* L;        // radiance gathered by this sample so far
-    uint4* meta;      // pixel, sample, depth, alive
+    uint2* meta;      // pixel | alive<<31, sample | depth<<24
     float4* sh_o;     // shadow queue: origin.xyz, t_max
     float4* sh_d;     // direction.xyz, slot bits
     float4* sh_c;     // contribution if unoccluded
@@ -63,7 +70,7 @@ struct SceneView {
     uint32_t n_objects, n_lights, n_nodes;
 };
 
-PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint4& meta) {
+PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
     uint32_t sample = f.sample_offset + (uint32_t)(w / f.npix);
     uint32_t pixel = (uint32_t)(w % f.npix);
     uint32_t x = pixel % f.cam.width, y = pixel / f.cam.width;
@@ -71,7 +78,7 @@ PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uin
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, u01(r.x), u01(r.y));   // world.rs:299
     ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
     rd = make_float4(d.x, d.y, d.z, 0.0f);
-    meta = make_uint4(pixel, sample, 0u, 1u);
+    meta = make_uint2(pixel | 0x80000000u, sample & 0x00ffffffu);
 }
 
 // K1 — initial fill of the pool
@@ -80,13 +87,13 @@ __global__ void __launch_bounds__(kBlock) k_generate(Pool pool, const __grid_con
     if (i >= pool.P) return;
     uint64_t w = work_base + i;
     if (w < f.total_work) {
-        float4 ro, rd; uint4 m;
+        float4 ro, rd; uint2 m;
         make_primary(f, w, ro, rd, m);
         pool.ray_o[i] = ro; pool.ray_d[i] = rd; pool.meta[i] = m;
         pool.beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
         pool.L[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     } else {
-        pool.meta[i] = make_uint4(0u, 0u, 0u, 0u);
+        pool.meta[i] = make_uint2(0u, 0u);
     }
 }
 
@@ -214,7 +221,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_closest(Pool pool, SceneView s
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, !BRUTE);
     uint32_t i = blockIdx.x * kBlock + threadIdx.x;
     if (i >= pool.P) return;
-    if (pool.meta[i].w == 0u) return;
+    if ((pool.meta[i].x >> 31) == 0u) return;
     float4 ro = pool.ray_o[i], rd = pool.ray_d[i];
     float t; int id;
     closest_hit<SMEM, BRUTE>(g, s.n_objects, v3(ro), v3(rd), t_min, t, id);
@@ -249,9 +256,10 @@ PT_DEV Compact block_compact(bool flag, uint64_t* counter, uint32_t* s_warp, uns
     if (lane == 0) s_warp[warp] = __popc(ballot);
     __syncthreads();
     if (warp == 0) {
-        uint32_t c = lane < kBlock / 32 ? s_warp[lane] : 0, x = c;
+        uint32_t nw = blockDim.x >> 5;
+        uint32_t c = lane < nw ? s_warp[lane] : 0, x = c;
         for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-        if (lane < kBlock / 32) s_warp[lane] = x - c;
+        if (lane < nw) s_warp[lane] = x - c;
         if (lane == 31) {
             *s_total = x;
             *s_base = x ? atomicAdd((unsigned long long*)counter, (unsigned long long)x) : 0ull;
@@ -273,35 +281,101 @@ PT_DEV float rr_prob(const Frame& f, float3 tn, uint32_t depth) {
     return l;
 }
 
+// meta packing: x = pixel | alive << 31, y = sample | depth << 24
+PT_DEV uint2 pack_meta(uint32_t pixel, uint32_t sample, uint32_t depth, bool alive) {
+    return make_uint2(pixel | (alive ? 0x80000000u : 0u), (sample & 0x00ffffffu) | (depth << 24));
+}
+#define META_ALIVE(m) (((m).x >> 31) != 0u)
+#define META_PIXEL(m) ((m).x & 0x7fffffffu)
+#define META_SAMPLE(m) ((m).y & 0x00ffffffu)
+#define META_DEPTH(m) ((m).y >> 24)
+
+enum { CLS_MIRROR = 0, CLS_DIFFUSE = 1, CLS_EMISSIVE = 2, CLS_MISS = 3, CLS_DEAD = 4, CLS_COUNT = 5 };
+
 // K4 + K6 + K7 (+ K8 accumulate, + K1 regeneration) for every live slot.
-__global__ void __launch_bounds__(kBlock) k_shade(Pool pool, SceneView s, const __grid_constant__ Frame f, uint64_t* __restrict__ counters,
-                                                  int iter_in_batch) {
-    __shared__ uint32_t s_warp[kBlock / 32];
+// The CTA's kShadeBlock path slots are staged through shared memory: ONE coalesced, vectorised load of the whole
+// path state up front and one coalesced store at the end; everything between works on the smem copy.
+// Phase 0: load + classify own slot (miss / emissive / diffuse / mirror / dead); the CTA counting-sorts its slots by
+//          class with warp ballots, so that phase A runs warps of (almost) one class.
+// Phase A: emission + look-ahead MIS resolve, NEE setup, BSDF sample, Russian roulette; survivors update their slot.
+// Phase B: the CTA's finished paths are compacted; the first `n_finished` threads accumulate them into the frame and
+//          re-seed their slots with new camera rays (coherent Philox + camera code instead of a divergent tail).
+__global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool pool, SceneView s, const __grid_constant__ Frame f,
+                                                                         uint64_t* __restrict__ counters, int iter_in_batch) {
+    constexpr int NW = kShadeBlock / 32;
+    __shared__ float4 s_ro[kShadeBlock], s_rd[kShadeBlock], s_beta[kShadeBlock], s_L[kShadeBlock];
+    __shared__ uint2 s_hit[kShadeBlock], s_meta[kShadeBlock];
+    __shared__ uint32_t s_warp[NW];
     __shared__ unsigned long long s_base;
     __shared__ uint32_t s_total;
-    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-    bool in_range = i < pool.P;
-    uint4 meta = in_range ? pool.meta[i] : make_uint4(0, 0, 0, 0);
-    const bool was_alive = meta.w != 0u;
-    bool alive = was_alive;
-    bool finished = false;           // path ended this iteration: accumulate + regenerate
-    bool emit_shadow = false;
-    float3 Lsum = v3(0.f, 0.f, 0.f);
+    __shared__ uint16_t s_cls_cnt[CLS_COUNT][NW];
+    __shared__ uint16_t s_order[kShadeBlock];
+    __shared__ uint16_t s_fin_slot[kShadeBlock];
+    __shared__ uint8_t s_dirty[kShadeBlock];   // bit0: ray/beta/meta changed, bit1: L changed
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t base = blockIdx.x * kShadeBlock;
+    const bool mis = f.strategy == PT_STRATEGY_MIS;
+
+    // ---- phase 0: coalesced load of the slot state, classify, counting sort by class
+    {
+        uint32_t i = base + tid;
+        uint32_t cls = CLS_DEAD;
+        uint2 m = make_uint2(0u, 0u);
+        if (i < pool.P) {
+            m = pool.meta[i];
+            uint2 h = pool.hit[i];
+            s_ro[tid] = pool.ray_o[i]; s_rd[tid] = pool.ray_d[i]; s_beta[tid] = pool.beta[i]; s_L[tid] = pool.L[i];
+            s_hit[tid] = h;
+            if (META_ALIVE(m)) {
+                if (h.y == 0xffffffffu) cls = CLS_MISS;
+                else {
+                    uint32_t kind = __float_as_uint(__ldg(s.mats + 2 * (size_t)h.y).w);
+                    cls = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
+                }
+            }
+        }
+        s_meta[tid] = m;
+        s_dirty[tid] = 0;
+        uint32_t my_rank = 0;
+#pragma unroll
+        for (uint32_t c = 0; c < CLS_COUNT; ++c) {
+            uint32_t b = __ballot_sync(0xffffffffu, cls == c);
+            if (lane == 0) s_cls_cnt[c][warp] = (uint16_t)__popc(b);
+            if (cls == c) my_rank = __popc(b & ((1u << lane) - 1));
+        }
+        __syncthreads();
+        if (tid < 32) {   // exclusive prefix over the CLS_COUNT x NW counts in (class, warp) order, one warp
+            uint32_t run = 0;
+            for (uint32_t k0 = 0; k0 < CLS_COUNT * NW; k0 += 32) {
+                uint32_t k = k0 + tid;
+                uint32_t v = k < CLS_COUNT * NW ? s_cls_cnt[k / NW][k % NW] : 0, x = v;
+                for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+                if (k < CLS_COUNT * NW) s_cls_cnt[k / NW][k % NW] = (uint16_t)(run + x - v);
+                run += __shfl_sync(0xffffffffu, x, 31);
+            }
+        }
+        __syncthreads();
+        s_order[s_cls_cnt[cls][warp] + my_rank] = (uint16_t)tid;
+        __syncthreads();
+    }
+
+    // ---- phase A (works on slot j of the smem copy)
+    const uint32_t j = s_order[tid];
+    const uint2 meta = s_meta[j];
+    bool alive = META_ALIVE(meta);
+    bool finished = false, emit_shadow = false;
     float3 sh_o = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
     float sh_tmax = 0.f;
     uint32_t n_vertex = 0, n_scatter = 0;
-    const bool mis = f.strategy == PT_STRATEGY_MIS;
-
     if (alive) {
-        float4 ro4 = pool.ray_o[i], rd4 = pool.ray_d[i];
-        uint2 h = pool.hit[i];
-        float3 ro = v3(ro4), rd = v3(rd4);
-        float3 beta = v3(pool.beta[i]);
-        const uint32_t depth = meta.z;
+        const uint2 h = s_hit[j];
+        const uint32_t depth = META_DEPTH(meta);
         if (h.y == 0xffffffffu) {
             finished = true;                                  // background is black, rendering.rs:140-141
-            Lsum = v3(pool.L[i]);
         } else {
+            const float4 ro4 = s_ro[j], rd4 = s_rd[j];
+            const float3 ro = v3(ro4), rd = v3(rd4);
+            const float3 beta = v3(s_beta[j]);
             const int obj = (int)h.y;
             const float t = __uint_as_float(h.x);
             float4 q0 = __ldg(s.prims + 4 * (size_t)obj), q1 = __ldg(s.prims + 4 * (size_t)obj + 1);
@@ -314,7 +388,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(Pool pool, SceneView s, const 
             float3 n = front ? n_out : -n_out;
             if (m.kind == PT_MATK_EMISSIVE && dot(m.color, m.color) > 0.0f) {
                 // rendering.rs:42-49 for a primary ray; :106-121 (look-ahead MIS) for a scattered ray
-                float3 L = v3(pool.L[i]);
+                float3 L = v3(s_L[j]);
                 if (depth == 0) L = m.color;
                 else if (!mis) L = L + beta * m.color;                // rendering.rs:226-228
                 else {
@@ -325,11 +399,12 @@ __global__ void __launch_bounds__(kBlock) k_shade(Pool pool, SceneView s, const 
                     L = L + beta * (m.color * (pb / (pb + ps)));
                 }
                 finished = true;
-                Lsum = L;
+                s_L[j] = make_float4(L.x, L.y, L.z, 0.f);
             } else {
                 n_vertex = 1;
-                uint4 b0 = philox4x32_10(meta.x, meta.y, depth, 0u, f.k0, f.k1);
-                uint4 b1 = philox4x32_10(meta.x, meta.y, depth, 1u, f.k0, f.k1);
+                const uint32_t pixel = META_PIXEL(meta), sample = META_SAMPLE(meta);
+                uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
+                uint4 b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
                 // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by K5
                 bool want_shadow = false;
                 if (mis && s.n_lights > 0) {
@@ -359,15 +434,14 @@ __global__ void __launch_bounds__(kBlock) k_shade(Pool pool, SceneView s, const 
                 float q = ok ? rr_prob(f, tn, depth) : 0.0f;
                 if (!ok || u01(b1.z) > q) {
                     finished = true;                                  // D of this vertex is dropped too (Q1)
-                    Lsum = v3(pool.L[i]);
                 } else {
                     emit_shadow = want_shadow;
                     float3 nb = tn / q;
-                    pool.beta[i] = make_float4(nb.x, nb.y, nb.z, 0.f);
-                    pool.ray_o[i] = make_float4(p.x, p.y, p.z, eta_new);      // rendering.rs:86-87
-                    pool.ray_d[i] = make_float4(wo.x, wo.y, wo.z, pdf);
-                    meta.z = depth + 1;
-                    pool.meta[i] = meta;
+                    s_beta[j] = make_float4(nb.x, nb.y, nb.z, 0.f);
+                    s_ro[j] = make_float4(p.x, p.y, p.z, eta_new);            // rendering.rs:86-87
+                    s_rd[j] = make_float4(wo.x, wo.y, wo.z, pdf);
+                    s_meta[j] = pack_meta(pixel, sample, depth + 1, true);
+                    s_dirty[j] = 1;
                     n_scatter = 1;
                 }
             }
@@ -378,38 +452,49 @@ __global__ void __launch_bounds__(kBlock) k_shade(Pool pool, SceneView s, const 
     if (emit_shadow) {
         uint32_t sidx = (uint32_t)cs.base + cs.rank;
         pool.sh_o[sidx] = make_float4(sh_o.x, sh_o.y, sh_o.z, sh_tmax);
-        pool.sh_d[sidx] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(i));
+        pool.sh_d[sidx] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(base + j));
         pool.sh_c[sidx] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
     }
-    // ---- K8 accumulate (world.rs:296-313: color_temp += ray_color)
-    if (finished) {
-        float lum = luminance(Lsum);
-        atomicAdd(f.accum + meta.x, make_float4(Lsum.x, Lsum.y, Lsum.z, lum * lum));
-    }
-    // ---- regeneration: finished slots take the next (pixel, sample) from the global work counter
+    // ---- phase B: compact finished paths, then accumulate (K8, world.rs:296-313) + regenerate coherently
     Compact cw = block_compact(finished, counters + C_WORK_NEXT, s_warp, &s_base, &s_total);
-    uint32_t n_primary = 0;
-    if (finished) {
-        uint64_t w = cw.base + cw.rank;
+    if (finished) s_fin_slot[cw.rank] = (uint16_t)j;
+    __syncthreads();
+    uint32_t n_primary = 0, n_dead = 0;
+    if (tid < cw.total) {
+        const uint32_t k = s_fin_slot[tid];
+        float4 L4 = s_L[k];
+        float lum = luminance(v3(L4));
+        atomicAdd(f.accum + META_PIXEL(s_meta[k]), make_float4(L4.x, L4.y, L4.z, lum * lum));
+        uint64_t w = cw.base + tid;
         if (w < f.total_work) {
-            float4 ro, rd; uint4 m;
+            float4 ro, rd; uint2 m;
             make_primary(f, w, ro, rd, m);
-            pool.ray_o[i] = ro; pool.ray_d[i] = rd; pool.meta[i] = m;
-            pool.beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
-            pool.L[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            s_ro[k] = ro; s_rd[k] = rd; s_meta[k] = m;
+            s_beta[k] = make_float4(1.f, 1.f, 1.f, 0.f);
+            s_L[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            s_dirty[k] = 3;
             n_primary = 1;
         } else {
-            alive = false;
-            pool.meta[i] = make_uint4(0u, 0u, 0u, 0u);
+            s_meta[k] = make_uint2(0u, 0u);
+            s_dirty[k] = 4;
+            n_dead = 1;
         }
     }
-    // ---- bookkeeping: live-slot count (one atomic per CTA) and per-CTA ray statistics (no atomics)
+    // ---- bookkeeping + coalesced write-back of the slots that changed
     uint32_t b_alive = __syncthreads_count(alive);
+    uint32_t b_dead = __syncthreads_count(n_dead);
     uint32_t b_vertex = __syncthreads_count(n_vertex);
     uint32_t b_scatter = __syncthreads_count(n_scatter);
     uint32_t b_primary = __syncthreads_count(n_primary);
-    if (threadIdx.x == 0) {
-        if (b_alive) atomicAdd((unsigned long long*)(counters + C_ALIVE_BASE + iter_in_batch), (unsigned long long)b_alive);
+    {
+        uint32_t i = base + tid;
+        uint32_t d = s_dirty[tid];
+        if (d & 1u) { pool.ray_o[i] = s_ro[tid]; pool.ray_d[i] = s_rd[tid]; pool.beta[i] = s_beta[tid]; }
+        if (d & 2u) pool.L[i] = s_L[tid];
+        if (d) pool.meta[i] = s_meta[tid];
+    }
+    if (tid == 0) {
+        if (b_alive > b_dead) atomicAdd((unsigned long long*)(counters + C_ALIVE_BASE + iter_in_batch), (unsigned long long)(b_alive - b_dead));
         uint4 st = pool.block_stats[blockIdx.x];
         st.x += b_primary; st.y += cs.total; st.z += b_scatter; st.w += b_vertex;
         pool.block_stats[blockIdx.x] = st;
@@ -562,8 +647,8 @@ int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_cam
 
 static int ensure_pool(pt_context* ctx, uint32_t P, Pool& pool) {
     uint32_t nblocks = (P + kBlock - 1) / kBlock;
-    size_t per_slot = 16 * 8 + 8 + 16;   // 8 float4 arrays + hit (uint2) + meta (uint4)
-    size_t bytes = per_slot * (size_t)P + 16 * (size_t)nblocks + 256 * 16;
+    size_t per_slot = 16 * 7 + 8 + 8;   // 7 float4 arrays + hit (uint2) + meta (uint2)
+    size_t bytes = per_slot * (size_t)P + 64 * (size_t)nblocks + 256 * 16;
     if (bytes > ctx->pool_bytes) {
         if (ctx->pool_mem) cudaFree(ctx->pool_mem);
         ctx->pool_mem = nullptr; ctx->pool_bytes = 0;
@@ -576,9 +661,9 @@ static int ensure_pool(pt_context* ctx, uint32_t P, Pool& pool) {
     pool.ray_o = (float4*)take(16 * (size_t)P); pool.ray_d = (float4*)take(16 * (size_t)P);
     pool.beta = (float4*)take(16 * (size_t)P); pool.L = (float4*)take(16 * (size_t)P);
     pool.sh_o = (float4*)take(16 * (size_t)P); pool.sh_d = (float4*)take(16 * (size_t)P); pool.sh_c = (float4*)take(16 * (size_t)P);
-    pool.meta = (uint4*)take(16 * (size_t)P);
+    pool.meta = (uint2*)take(8 * (size_t)P);
     pool.hit = (uint2*)take(8 * (size_t)P);
-    pool.block_stats = (uint4*)take(16 * (size_t)nblocks);
+    pool.block_stats = (uint4*)take(16 * (size_t)nblocks * 4);
     return PT_OK;
 }
 
@@ -607,7 +692,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #undef SETS
     uint64_t first = (uint64_t)P < f.total_work ? (uint64_t)P : f.total_work;
     PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_counters + C_WORK_NEXT, &first, 8, cudaMemcpyHostToDevice, st));
-    PT_CUDA_CHECK(ctx, cudaMemsetAsync(pool.block_stats, 0, 16 * (size_t)grid, st));
+    const uint32_t sgrid = P / kShadeBlock;
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(pool.block_stats, 0, 16 * (size_t)sgrid, st));
     const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
     float ms_k[PT_K_COUNT] = {0, 0, 0, 0};
     uint32_t n_k[PT_K_COUNT] = {0, 0, 0, 0};
@@ -639,7 +725,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
             prof_end();
 #undef TRACE
             prof_begin(PT_K_SHADE);
-            k_shade<<<grid, kBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
+            k_shade<<<P / kShadeBlock, kShadeBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
             prof_end();
             launches += 2;
             if (mis) {
@@ -659,8 +745,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     }
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     if (stats) {
-        std::vector<uint4> bs(grid);
-        PT_CUDA_CHECK(ctx, cudaMemcpy(bs.data(), pool.block_stats, 16 * (size_t)grid, cudaMemcpyDeviceToHost));
+        std::vector<uint4> bs(sgrid);
+        PT_CUDA_CHECK(ctx, cudaMemcpy(bs.data(), pool.block_stats, 16 * (size_t)sgrid, cudaMemcpyDeviceToHost));
         uint64_t a = 0, b = 0, c = 0, d = 0;
         for (auto& v : bs) { a += v.x; b += v.y; c += v.z; d += v.w; }
         stats->samples = f.total_work;

@@ -94,7 +94,7 @@ def test_render_smoke_matches_oracle_mean(oracle, gpu_ctx):
     sc.close()
     assert np.isfinite(rad).all()
     assert st["samples"] == 64 * 64 * spp_g
-    r = oracle.render(ocam, sh, mt, oracle.RenderParams(spp=spp_c, seed=123), "f64", recursive=True)
+    r = oracle.render(ocam, sh, mt, oracle.RenderParams(spp=spp_c, seed=123), "f64", recursive=False)   # iterative form counts vertices
     mean_c = r["sum"] / spp_c
     var_c = np.maximum(r["sumsq"] / spp_c - mean_c ** 2, 0)
     se2 = var_c / spp_c + var_c / spp_g
