@@ -98,7 +98,7 @@ int32_t pt_render(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, 
                   float* radiance_rgb, uint8_t* rgba8, pt_stats* stats_or_null);
 
 /* Device-resident variant for the multi-GPU spp split: ADDS this call's samples into d_accum (device pointer,
- * W*H float4 = {sum r, sum g, sum b, sum luminance^2}); caller zeroes it, reduces it across ranks and resolves it. */
+ * W*H float4 = {sum r, sum g, sum b, reserved}); caller zeroes it, reduces it across ranks and resolves it. */
 int32_t pt_render_accumulate_device(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p,
                                     void* d_accum_f4, pt_stats* stats_or_null);
 /* mean = sum / total_spp; writes d_radiance_rgb (W*H*3 floats, may be null) and d_rgba8 (W*H*4 bytes, may be null). */

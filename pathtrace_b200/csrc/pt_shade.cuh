@@ -174,7 +174,9 @@ PT_DEV float3 orennayar_f(const Mat& m, float3 rd, float3 o, float3 n) {
 PT_DEV void bsdf_eval(const Mat& m, float3 rd, float eta, float3 o, float3 n, float3& f, float& pdf) {
     switch (m.kind) {
         case PT_MATK_LAMBERT: f = m.color * PT_INV_PI; pdf = fmaxf(dot(o, n), 0.0f) * PT_INV_PI; break;
+#ifndef PT_EXPERIMENT_NO_MIRROR
         case PT_MATK_MIRROR: mirror_eval(m, rd, eta, o, n, f, pdf); break;
+#endif
         case PT_MATK_ORENNAYAR: f = orennayar_f(m, rd, o, n); pdf = fmaxf(dot(o, n), 0.0f) * PT_INV_PI; break;
         default: f = v3(0.f, 0.f, 0.f); pdf = 1.0f; break;
     }
@@ -182,7 +184,9 @@ PT_DEV void bsdf_eval(const Mat& m, float3 rd, float eta, float3 o, float3 n, fl
 // Material::bsdf_pdf_sample (default material.rs:29-40; Mirror override mirror.rs:200-305)
 PT_DEV bool bsdf_sample(const Mat& m, float3 rd, float eta, float3 n, float r1, float r2, float r3, float3& dir, float3& f,
                         float& pdf, float& cos_theta) {
+#ifndef PT_EXPERIMENT_NO_MIRROR
     if (m.kind == PT_MATK_MIRROR) return mirror_sample(m, rd, eta, n, r1, r2, r3, dir, f, pdf, cos_theta);
+#endif
     if (m.kind == PT_MATK_EMISSIVE) return false;   // f = 0: zero throughput (never reached in MIS, rendering.rs:42-49)
     dir = cosine_sample(n, r1, r2);
     cos_theta = fmaxf(dot(dir, n), 0.0f);

@@ -27,16 +27,22 @@ constexpr int kBlock = 256;
 #ifndef PT_SHADE_BLOCK
 #define PT_SHADE_BLOCK 256
 #endif
+#ifndef PT_SHADE_SLOTS
+#define PT_SHADE_SLOTS 1024
+#endif
 #ifndef PT_SHADE_MIN_BLOCKS
-#define PT_SHADE_MIN_BLOCKS 3
+#define PT_SHADE_MIN_BLOCKS 4
 #endif
 constexpr int kShadeBlock = PT_SHADE_BLOCK, kShadeMinBlocks = PT_SHADE_MIN_BLOCKS;
+constexpr int kShadeSlots = PT_SHADE_SLOTS;   // path slots owned by one shade CTA (a multiple of kShadeBlock and of kBlock)
 constexpr int kItersPerBatch = 16;
 constexpr int kStackDepth = 64;
 constexpr uint32_t kMaxSmemPrims = 1024;   // scene staged in shared memory up to this many objects
 
 // device counter block (uint64 words)
-enum { C_WORK_NEXT = 0, C_SHADOW_BASE = 1, C_ALIVE_BASE = C_SHADOW_BASE + kItersPerBatch, C_TOTAL = C_ALIVE_BASE + kItersPerBatch };
+// device counter block (uint64 words); every counter sits in its own 256-byte line so their L2 atomics do not serialise
+enum { C_STRIDE = 32, C_WORK_NEXT = 0, C_SHADOW_BASE = C_STRIDE, C_ALIVE_BASE = C_SHADOW_BASE + kItersPerBatch * C_STRIDE,
+       C_TOTAL = C_ALIVE_BASE + kItersPerBatch * C_STRIDE };
 
 struct Pool {
     uint32_t P;
@@ -44,22 +50,24 @@ struct Pool {
     float4* ray_d;    // direction.xyz, bsdf pdf of the scatter that produced the ray (MIS at look-ahead)
     uint2* hit;       // t bits, object id (0xffffffff = miss)
     float4* beta;     // path throughput rgb
-    float4* L;        // radiance gathered by this sample so far
     uint2* meta;      // pixel | alive<<31, sample | depth<<24
     float4* sh_o;     // shadow queue: origin.xyz, t_max
     float4* sh_d;     // direction.xyz, slot bits
     float4* sh_c;     // contribution if unoccluded
     uint4* block_stats;   // per-CTA: primary, shadow, scattered, vertices (no atomics)
+    uint32_t* seg_count;  // per shade-CTA: shadow rays emitted this iteration (its private segment of the shadow queue)
+    unsigned long long* block_next;   // per shade-CTA: next work item of its private, contiguous work range
 };
 
 struct Frame {
     CameraDev cam;
     uint32_t npix;
     uint64_t total_work;     // npix * spp of this call
+    uint64_t chunk;          // work items owned by each shade-CTA (contiguous range)
     uint32_t sample_offset, min_depth, max_depth, strategy;
     uint32_t k0, k1;         // Philox key
     float t_min;
-    float4* accum;           // per pixel: sum r, g, b, sum luminance^2
+    float4* accum;           // per pixel: sum r, g, b, (reserved)
 };
 
 struct SceneView {
@@ -81,17 +89,24 @@ PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uin
     meta = make_uint2(pixel | 0x80000000u, sample & 0x00ffffffu);
 }
 
-// K1 — initial fill of the pool
-__global__ void __launch_bounds__(kBlock) k_generate(Pool pool, const __grid_constant__ Frame f, uint64_t work_base) {
-    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+// K1 — initial fill of the pool.  Work is partitioned statically: shade-CTA b owns the contiguous work range
+// [b*chunk, (b+1)*chunk) and hands it out to its own kShadeBlock slots (no global work counter, no global atomics).
+__global__ void __launch_bounds__(kBlock) k_generate(Pool pool, const __grid_constant__ Frame f) {
+    const uint32_t seg = blockIdx.x / (kShadeSlots / kBlock), l = (blockIdx.x % (kShadeSlots / kBlock)) * kBlock + threadIdx.x;
+    const uint32_t i = seg * kShadeSlots + l;
+    uint64_t lo = (uint64_t)seg * f.chunk, hi = lo + f.chunk < f.total_work ? lo + f.chunk : f.total_work;
+    uint64_t w = lo + l;
+    if (l == 0) {
+        pool.block_next[seg] = lo + kShadeSlots;
+        uint64_t avail = hi > lo ? hi - lo : 0;
+        pool.block_stats[seg] = make_uint4((uint32_t)(avail < kShadeSlots ? avail : kShadeSlots), 0u, 0u, 0u);
+    }
     if (i >= pool.P) return;
-    uint64_t w = work_base + i;
-    if (w < f.total_work) {
+    if (w < hi) {
         float4 ro, rd; uint2 m;
         make_primary(f, w, ro, rd, m);
         pool.ray_o[i] = ro; pool.ray_d[i] = rd; pool.meta[i] = m;
         pool.beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
-        pool.L[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     } else {
         pool.meta[i] = make_uint2(0u, 0u);
     }
@@ -228,20 +243,21 @@ __global__ void __launch_bounds__(kBlock) k_trace_closest(Pool pool, SceneView s
     pool.hit[i] = make_uint2(__float_as_uint(t), (uint32_t)id);
 }
 
-// K5 — any-hit over the compacted shadow queue; unoccluded entries add their contribution to the slot's L
+// K5 — any-hit over the shadow queue.  The queue is compacted per shade-CTA (ballot/popc + shared-memory atomics):
+// segment b holds seg_count[b] dense entries, so every warp here is full except the last one of a segment.
 template <bool SMEM, bool BRUTE>
-__global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s, float t_min, const uint64_t* __restrict__ count) {
+__global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s, float t_min, float4* __restrict__ accum) {
     extern __shared__ float4 smem[];
-    uint32_t n = (uint32_t)*count;
-    if (blockIdx.x * kBlock >= n) return;
+    const uint32_t seg = blockIdx.x / (kShadeSlots / kBlock), l0 = (blockIdx.x % (kShadeSlots / kBlock)) * kBlock;
+    const uint32_t n = pool.seg_count[seg];
+    if (l0 >= n) return;
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, !BRUTE);
-    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
-    if (i >= n) return;
+    if (l0 + threadIdx.x >= n) return;
+    uint32_t i = seg * kShadeSlots + l0 + threadIdx.x;
     float4 o = pool.sh_o[i], d = pool.sh_d[i];
     if (!any_hit<SMEM, BRUTE>(g, s.n_objects, v3(o), v3(d), t_min, o.w)) {
-        uint32_t slot = __float_as_uint(d.w);
-        float4 c = pool.sh_c[i], L = pool.L[slot];
-        pool.L[slot] = make_float4(L.x + c.x, L.y + c.y, L.z + c.z, 0.f);
+        float4 c = pool.sh_c[i];                       // K8: color_temp += ..., world.rs:296-313
+        atomicAdd(accum + __float_as_uint(d.w), make_float4(c.x, c.y, c.z, 0.f));
     }
 }
 
@@ -292,211 +308,229 @@ PT_DEV uint2 pack_meta(uint32_t pixel, uint32_t sample, uint32_t depth, bool ali
 
 enum { CLS_MIRROR = 0, CLS_DIFFUSE = 1, CLS_EMISSIVE = 2, CLS_MISS = 3, CLS_DEAD = 4, CLS_COUNT = 5 };
 
-// K4 + K6 + K7 (+ K8 accumulate, + K1 regeneration) for every live slot.
-// The CTA's kShadeBlock path slots are staged through shared memory: ONE coalesced, vectorised load of the whole
-// path state up front and one coalesced store at the end; everything between works on the smem copy.
-// Phase 0: load + classify own slot (miss / emissive / diffuse / mirror / dead); the CTA counting-sorts its slots by
-//          class with warp ballots, so that phase A runs warps of (almost) one class.
-// Phase A: emission + look-ahead MIS resolve, NEE setup, BSDF sample, Russian roulette; survivors update their slot.
-// Phase B: the CTA's finished paths are compacted; the first `n_finished` threads accumulate them into the frame and
-//          re-seed their slots with new camera rays (coherent Philox + camera code instead of a divergent tail).
+// K4 + K6 + K7 (+ K8 accumulate, + K1 regeneration).
+// Work per path varies by an order of magnitude (miss ~ nothing, diffuse vertex ~ 500 instructions, GGX vertex ~ 1400), so
+// a CTA owns kShadeSlots (> its thread count) path slots and schedules them dynamically:
+// Phase 0: coalesced load of (meta, hit) of all its slots into shared memory; every slot is classified
+//          (mirror / diffuse / emissive / miss / dead) and the CTA counting-sorts the slot list by class, heaviest
+//          class first, with warp ballots + popc.
+// Phase A: warps pull TILES of 32 consecutive entries of the sorted list from a shared-memory counter until none is left
+//          (longest-processing-time-first list scheduling): a tile is (almost always) one class, so warps run coherent
+//          code, and no warp idles behind a GGX warp.  Per tile: emission / look-ahead MIS resolve, NEE setup, BSDF sample,
+//          Russian roulette; shadow rays are compacted (ballot/popc + one shared atomic per warp) into the CTA's private
+//          segment of the shadow queue; finished paths are accumulated into the frame and their slots re-seeded from the
+//          CTA's private contiguous work range.  No global atomics except the per-pixel accumulate.
 __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool pool, SceneView s, const __grid_constant__ Frame f,
                                                                          uint64_t* __restrict__ counters, int iter_in_batch) {
     constexpr int NW = kShadeBlock / 32;
-    __shared__ float4 s_ro[kShadeBlock], s_rd[kShadeBlock], s_beta[kShadeBlock], s_L[kShadeBlock];
-    __shared__ uint2 s_hit[kShadeBlock], s_meta[kShadeBlock];
-    __shared__ uint32_t s_warp[NW];
-    __shared__ unsigned long long s_base;
-    __shared__ uint32_t s_total;
-    __shared__ uint16_t s_cls_cnt[CLS_COUNT][NW];
-    __shared__ uint16_t s_order[kShadeBlock];
-    __shared__ uint16_t s_fin_slot[kShadeBlock];
-    __shared__ uint8_t s_dirty[kShadeBlock];   // bit0: ray/beta/meta changed, bit1: L changed
+    constexpr int SPT = kShadeSlots / kShadeBlock;      // slots classified per thread
+    constexpr int NTILES = kShadeSlots / 32;
+    __shared__ uint2 s_hit[kShadeSlots], s_meta[kShadeSlots];
+    __shared__ uint16_t s_cls_cnt[CLS_COUNT][SPT * NW];
+    __shared__ uint16_t s_order[kShadeSlots];
+    __shared__ uint32_t s_stats[5];            // primary, shadow(unused), scattered, vertices, alive
+    __shared__ unsigned long long s_next;      // this CTA's next work item
+    __shared__ uint32_t s_shadow;              // entries in this CTA's shadow-queue segment
+    __shared__ uint32_t s_tile;                // next tile of the sorted list
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t base = blockIdx.x * kShadeBlock;
+    const uint32_t base = blockIdx.x * kShadeSlots;
     const bool mis = f.strategy == PT_STRATEGY_MIS;
+    const uint64_t work_lo = (uint64_t)blockIdx.x * f.chunk, work_hi = work_lo + f.chunk < f.total_work ? work_lo + f.chunk : f.total_work;
 
-    // ---- phase 0: coalesced load of the slot state, classify, counting sort by class
+    // ---- phase 0
     {
-        uint32_t i = base + tid;
-        uint32_t cls = CLS_DEAD;
-        uint2 m = make_uint2(0u, 0u);
-        if (i < pool.P) {
-            m = pool.meta[i];
-            uint2 h = pool.hit[i];
-            s_ro[tid] = pool.ray_o[i]; s_rd[tid] = pool.ray_d[i]; s_beta[tid] = pool.beta[i]; s_L[tid] = pool.L[i];
-            s_hit[tid] = h;
-            if (META_ALIVE(m)) {
-                if (h.y == 0xffffffffu) cls = CLS_MISS;
-                else {
-                    uint32_t kind = __float_as_uint(__ldg(s.mats + 2 * (size_t)h.y).w);
-                    cls = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
+        uint32_t cls[SPT], rank[SPT];
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            uint32_t l = k * kShadeBlock + tid, i = base + l;
+            uint32_t c = CLS_DEAD;
+            uint2 m = make_uint2(0u, 0u), h = make_uint2(0u, 0xffffffffu);
+            if (i < pool.P) {
+                m = pool.meta[i];
+                h = pool.hit[i];
+                if (META_ALIVE(m)) {
+                    if (h.y == 0xffffffffu) c = CLS_MISS;
+                    else {
+                        uint32_t kind = __float_as_uint(__ldg(s.mats + 2 * (size_t)h.y).w);
+                        c = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
+                    }
                 }
             }
-        }
-        s_meta[tid] = m;
-        s_dirty[tid] = 0;
-        uint32_t my_rank = 0;
+            s_meta[l] = m; s_hit[l] = h;
+            cls[k] = c; rank[k] = 0;
 #pragma unroll
-        for (uint32_t c = 0; c < CLS_COUNT; ++c) {
-            uint32_t b = __ballot_sync(0xffffffffu, cls == c);
-            if (lane == 0) s_cls_cnt[c][warp] = (uint16_t)__popc(b);
-            if (cls == c) my_rank = __popc(b & ((1u << lane) - 1));
+            for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) {
+                uint32_t b = __ballot_sync(0xffffffffu, c == cc);
+                if (lane == 0) s_cls_cnt[cc][k * NW + warp] = (uint16_t)__popc(b);
+                if (c == cc) rank[k] = __popc(b & ((1u << lane) - 1));
+            }
         }
+        if (tid < 5) s_stats[tid] = 0;
+        if (tid == 0) { s_next = pool.block_next[blockIdx.x]; s_shadow = 0; s_tile = 0; }
         __syncthreads();
-        if (tid < 32) {   // exclusive prefix over the CLS_COUNT x NW counts in (class, warp) order, one warp
+        if (tid < 32) {   // exclusive prefix over the CLS_COUNT x (SPT*NW) counts in (class, group) order, one warp
+            constexpr uint32_t N = CLS_COUNT * SPT * NW;
+            uint16_t* flat = &s_cls_cnt[0][0];
             uint32_t run = 0;
-            for (uint32_t k0 = 0; k0 < CLS_COUNT * NW; k0 += 32) {
+            for (uint32_t k0 = 0; k0 < N; k0 += 32) {
                 uint32_t k = k0 + tid;
-                uint32_t v = k < CLS_COUNT * NW ? s_cls_cnt[k / NW][k % NW] : 0, x = v;
+                uint32_t v = k < N ? flat[k] : 0, x = v;
                 for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-                if (k < CLS_COUNT * NW) s_cls_cnt[k / NW][k % NW] = (uint16_t)(run + x - v);
+                if (k < N) flat[k] = (uint16_t)(run + x - v);
                 run += __shfl_sync(0xffffffffu, x, 31);
             }
         }
         __syncthreads();
-        s_order[s_cls_cnt[cls][warp] + my_rank] = (uint16_t)tid;
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) s_order[s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)(k * kShadeBlock + tid);
         __syncthreads();
     }
 
-    // ---- phase A (works on slot j of the smem copy)
-    const uint32_t j = s_order[tid];
-    const uint2 meta = s_meta[j];
-    bool alive = META_ALIVE(meta);
-    bool finished = false, emit_shadow = false;
-    float3 sh_o = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
-    float sh_tmax = 0.f;
-    uint32_t n_vertex = 0, n_scatter = 0;
-    if (alive) {
-        const uint2 h = s_hit[j];
-        const uint32_t depth = META_DEPTH(meta);
-        if (h.y == 0xffffffffu) {
-            finished = true;                                  // background is black, rendering.rs:140-141
-        } else {
-            const float4 ro4 = s_ro[j], rd4 = s_rd[j];
-            const float3 ro = v3(ro4), rd = v3(rd4);
-            const float3 beta = v3(s_beta[j]);
-            const int obj = (int)h.y;
-            const float t = __uint_as_float(h.x);
-            float4 q0 = __ldg(s.prims + 4 * (size_t)obj), q1 = __ldg(s.prims + 4 * (size_t)obj + 1);
-            float4 q2 = __ldg(s.prims + 4 * (size_t)obj + 2), q3 = __ldg(s.prims + 4 * (size_t)obj + 3);
-            Mat m = load_mat(s.mats, obj);
-            float3 p = ro + rd * t;
-            const bool is_tri = __float_as_uint(q0.w) == PT_KIND_TRIANGLE;
-            float3 n_out = is_tri ? v3(q3) : (p - v3(q0)) / q1.x;     // shape.rs:195 / :86
-            const bool front = dot(rd, n_out) < 0.0f;                 // base.rs:20
-            float3 n = front ? n_out : -n_out;
-            if (m.kind == PT_MATK_EMISSIVE && dot(m.color, m.color) > 0.0f) {
-                // rendering.rs:42-49 for a primary ray; :106-121 (look-ahead MIS) for a scattered ray
-                float3 L = v3(s_L[j]);
-                if (depth == 0) L = m.color;
-                else if (!mis) L = L + beta * m.color;                // rendering.rs:226-228
-                else {
-                    float ps;                                         // shape pdf from the previous vertex, NOT / n_lights (Q2)
-                    if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), ro, p, ld, dd); }
-                    else ps = sphere_pdf_omega(v3(q0), q1.x, ro);
-                    float pb = rd4.w;
-                    L = L + beta * (m.color * (pb / (pb + ps)));
-                }
-                finished = true;
-                s_L[j] = make_float4(L.x, L.y, L.z, 0.f);
+    // ---- phase A: dynamic tiles
+    uint32_t c_primary = 0, c_scatter = 0, c_vertex = 0, c_alive = 0;
+    while (true) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(&s_tile, 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= NTILES) break;
+        const uint32_t j = s_order[tile * 32 + lane];
+        const uint32_t i = base + j;
+        const uint2 meta = s_meta[j];
+        bool alive = META_ALIVE(meta);
+        if (!__any_sync(0xffffffffu, alive)) break;          // sorted: dead slots are last
+        bool finished = false, emit_shadow = false;
+        bool add_L = false;
+        float3 Ladd = v3(0.f, 0.f, 0.f);
+        float3 sh_o = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
+        float sh_tmax = 0.f;
+        if (alive) {
+            const uint2 h = s_hit[j];
+            const uint32_t depth = META_DEPTH(meta);
+            if (h.y == 0xffffffffu) {
+                finished = true;                                  // background is black, rendering.rs:140-141
             } else {
-                n_vertex = 1;
-                const uint32_t pixel = META_PIXEL(meta), sample = META_SAMPLE(meta);
-                uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
-                uint4 b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
-                // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by K5
-                bool want_shadow = false;
-                if (mis && s.n_lights > 0) {
-                    uint32_t li = __ldg(s.light_ids + urange(b0.x, s.n_lights));
-                    float4 l0 = __ldg(s.prims + 4 * (size_t)li), l1 = __ldg(s.prims + 4 * (size_t)li + 1);
-                    float4 l2 = __ldg(s.prims + 4 * (size_t)li + 2), l3 = __ldg(s.prims + 4 * (size_t)li + 3);
-                    float3 le = v3(__ldg(s.mats + 2 * (size_t)li));
-                    float3 ldir; float dist, pdf_shape;
-                    sample_light_shape(l0, l1, l2, l3, p, u01(b0.y), u01(b0.z), ldir, dist, pdf_shape);
-                    float pl = pdf_shape / (float)s.n_lights;         // world.rs:260
-                    float cos_theta = fabsf(dot(n, ldir));            // rendering.rs:68
-                    float3 fe; float pb;
-                    bsdf_eval(m, rd, ro4.w, ldir, n, fe, pb);         // inherited eta_ratio (Q3)
-                    float w_nee = pl / (pl + pb);
-                    float3 c = beta * fe * le * (w_nee * cos_theta / pl);
-                    if (finite3(c) && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
-                        want_shadow = true;
-                        sh_o = p; sh_d = ldir; sh_c = c; sh_tmax = dist - 0.001f;   // rendering.rs:64
+                const float4 ro4 = pool.ray_o[i], rd4 = pool.ray_d[i];
+                const float3 ro = v3(ro4), rd = v3(rd4);
+                const float3 beta = v3(pool.beta[i]);
+                const int obj = (int)h.y;
+                const float t = __uint_as_float(h.x);
+                float4 q0 = __ldg(s.prims + 4 * (size_t)obj), q1 = __ldg(s.prims + 4 * (size_t)obj + 1);
+                float4 q2 = __ldg(s.prims + 4 * (size_t)obj + 2), q3 = __ldg(s.prims + 4 * (size_t)obj + 3);
+                Mat m = load_mat(s.mats, obj);
+                float3 p = ro + rd * t;
+                const bool is_tri = __float_as_uint(q0.w) == PT_KIND_TRIANGLE;
+                float3 n_out = is_tri ? v3(q3) : (p - v3(q0)) / q1.x;     // shape.rs:195 / :86
+                const bool front = dot(rd, n_out) < 0.0f;                 // base.rs:20
+                float3 n = front ? n_out : -n_out;
+                if (m.kind == PT_MATK_EMISSIVE && dot(m.color, m.color) > 0.0f) {
+                    // rendering.rs:42-49 for a primary ray; :106-121 (look-ahead MIS) for a scattered ray
+                    float3 L;
+                    if (depth == 0) L = m.color;
+                    else if (!mis) L = beta * m.color;                    // rendering.rs:226-228
+                    else {
+                        float ps;                                         // shape pdf from the previous vertex, NOT / n_lights (Q2)
+                        if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), ro, p, ld, dd); }
+                        else ps = sphere_pdf_omega(v3(q0), q1.x, ro);
+                        float pb = rd4.w;
+                        L = beta * (m.color * (pb / (pb + ps)));
                     }
-                }
-                // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
-                float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
-                float3 wo, fs; float pdf, cos_s;
-                bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.w), u01(b1.x), u01(b1.y), wo, fs, pdf, cos_s);
-                float3 tn = beta * fs * (cos_s / pdf);
-                ok = ok && finite3(tn);
-                float q = ok ? rr_prob(f, tn, depth) : 0.0f;
-                if (!ok || u01(b1.z) > q) {
-                    finished = true;                                  // D of this vertex is dropped too (Q1)
+                    finished = true;
+                    add_L = true; Ladd = L;
                 } else {
-                    emit_shadow = want_shadow;
-                    float3 nb = tn / q;
-                    s_beta[j] = make_float4(nb.x, nb.y, nb.z, 0.f);
-                    s_ro[j] = make_float4(p.x, p.y, p.z, eta_new);            // rendering.rs:86-87
-                    s_rd[j] = make_float4(wo.x, wo.y, wo.z, pdf);
-                    s_meta[j] = pack_meta(pixel, sample, depth + 1, true);
-                    s_dirty[j] = 1;
-                    n_scatter = 1;
+                    c_vertex++;
+                    const uint32_t pixel = META_PIXEL(meta), sample = META_SAMPLE(meta);
+                    uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
+                    uint4 b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
+                    // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by K5
+                    bool want_shadow = false;
+                    if (mis && s.n_lights > 0) {
+                        uint32_t li = __ldg(s.light_ids + urange(b0.x, s.n_lights));
+                        float4 l0 = __ldg(s.prims + 4 * (size_t)li), l1 = __ldg(s.prims + 4 * (size_t)li + 1);
+                        float4 l2 = __ldg(s.prims + 4 * (size_t)li + 2), l3 = __ldg(s.prims + 4 * (size_t)li + 3);
+                        float3 le = v3(__ldg(s.mats + 2 * (size_t)li));
+                        float3 ldir; float dist, pdf_shape;
+                        sample_light_shape(l0, l1, l2, l3, p, u01(b0.y), u01(b0.z), ldir, dist, pdf_shape);
+                        float pl = pdf_shape / (float)s.n_lights;         // world.rs:260
+                        float cos_theta = fabsf(dot(n, ldir));            // rendering.rs:68
+                        float3 fe; float pb;
+                        bsdf_eval(m, rd, ro4.w, ldir, n, fe, pb);         // inherited eta_ratio (Q3)
+                        float w_nee = pl / (pl + pb);
+                        float3 c = beta * fe * le * (w_nee * cos_theta / pl);
+                        if (finite3(c) && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
+                            want_shadow = true;
+                            sh_o = p; sh_d = ldir; sh_c = c; sh_tmax = dist - 0.001f;   // rendering.rs:64
+                        }
+                    }
+                    // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
+                    float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
+                    float3 wo, fs; float pdf, cos_s;
+                    bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.w), u01(b1.x), u01(b1.y), wo, fs, pdf, cos_s);
+                    float3 tn = beta * fs * (cos_s / pdf);
+                    ok = ok && finite3(tn);
+                    float q = ok ? rr_prob(f, tn, depth) : 0.0f;
+                    if (!ok || u01(b1.z) > q) {
+                        finished = true;                                  // D of this vertex is dropped too (Q1)
+                    } else {
+                        emit_shadow = want_shadow;
+                        float3 nb = tn / q;
+                        pool.beta[i] = make_float4(nb.x, nb.y, nb.z, 0.f);
+                        pool.ray_o[i] = make_float4(p.x, p.y, p.z, eta_new);      // rendering.rs:86-87
+                        pool.ray_d[i] = make_float4(wo.x, wo.y, wo.z, pdf);
+                        pool.meta[i] = pack_meta(pixel, sample, depth + 1, true);
+                        c_scatter++;
+                    }
                 }
             }
         }
-    }
-    // ---- shadow queue compaction (ballot/popc + one atomic per CTA)
-    Compact cs = block_compact(emit_shadow, counters + C_SHADOW_BASE + iter_in_batch, s_warp, &s_base, &s_total);
-    if (emit_shadow) {
-        uint32_t sidx = (uint32_t)cs.base + cs.rank;
-        pool.sh_o[sidx] = make_float4(sh_o.x, sh_o.y, sh_o.z, sh_tmax);
-        pool.sh_d[sidx] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(base + j));
-        pool.sh_c[sidx] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
-    }
-    // ---- phase B: compact finished paths, then accumulate (K8, world.rs:296-313) + regenerate coherently
-    Compact cw = block_compact(finished, counters + C_WORK_NEXT, s_warp, &s_base, &s_total);
-    if (finished) s_fin_slot[cw.rank] = (uint16_t)j;
-    __syncthreads();
-    uint32_t n_primary = 0, n_dead = 0;
-    if (tid < cw.total) {
-        const uint32_t k = s_fin_slot[tid];
-        float4 L4 = s_L[k];
-        float lum = luminance(v3(L4));
-        atomicAdd(f.accum + META_PIXEL(s_meta[k]), make_float4(L4.x, L4.y, L4.z, lum * lum));
-        uint64_t w = cw.base + tid;
-        if (w < f.total_work) {
-            float4 ro, rd; uint2 m;
-            make_primary(f, w, ro, rd, m);
-            s_ro[k] = ro; s_rd[k] = rd; s_meta[k] = m;
-            s_beta[k] = make_float4(1.f, 1.f, 1.f, 0.f);
-            s_L[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-            s_dirty[k] = 3;
-            n_primary = 1;
-        } else {
-            s_meta[k] = make_uint2(0u, 0u);
-            s_dirty[k] = 4;
-            n_dead = 1;
+        // ---- shadow queue compaction into this CTA's segment: warp ballot/popc + one shared-memory atomic per warp
+        {
+            uint32_t bal = __ballot_sync(0xffffffffu, emit_shadow);
+            uint32_t sbase = 0;
+            if (lane == 0 && bal) sbase = atomicAdd(&s_shadow, (uint32_t)__popc(bal));
+            sbase = __shfl_sync(0xffffffffu, sbase, 0);
+            if (emit_shadow) {
+                uint32_t sidx = base + sbase + __popc(bal & ((1u << lane) - 1));
+                pool.sh_o[sidx] = make_float4(sh_o.x, sh_o.y, sh_o.z, sh_tmax);
+                pool.sh_d[sidx] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(META_PIXEL(meta)));
+                pool.sh_c[sidx] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
+            }
         }
+        // ---- K8 accumulate (world.rs:296-313) + regeneration from this CTA's private work range
+        {
+            uint32_t bal = __ballot_sync(0xffffffffu, finished);
+            unsigned long long wbase = 0;
+            if (lane == 0 && bal) wbase = atomicAdd(&s_next, (unsigned long long)__popc(bal));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (finished) {
+                if (add_L) atomicAdd(f.accum + META_PIXEL(meta), make_float4(Ladd.x, Ladd.y, Ladd.z, 0.f));
+                uint64_t w = wbase + __popc(bal & ((1u << lane) - 1));
+                if (w < work_hi) {
+                    float4 ro, rd; uint2 m;
+                    make_primary(f, w, ro, rd, m);
+                    pool.ray_o[i] = ro; pool.ray_d[i] = rd; pool.meta[i] = m;
+                    pool.beta[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+                    c_primary++;
+                } else {
+                    pool.meta[i] = make_uint2(0u, 0u);
+                    alive = false;
+                }
+            }
+        }
+        c_alive += alive ? 1u : 0u;
     }
-    // ---- bookkeeping + coalesced write-back of the slots that changed
-    uint32_t b_alive = __syncthreads_count(alive);
-    uint32_t b_dead = __syncthreads_count(n_dead);
-    uint32_t b_vertex = __syncthreads_count(n_vertex);
-    uint32_t b_scatter = __syncthreads_count(n_scatter);
-    uint32_t b_primary = __syncthreads_count(n_primary);
+    // ---- bookkeeping: warp reductions -> shared atomics -> one global update per CTA
     {
-        uint32_t i = base + tid;
-        uint32_t d = s_dirty[tid];
-        if (d & 1u) { pool.ray_o[i] = s_ro[tid]; pool.ray_d[i] = s_rd[tid]; pool.beta[i] = s_beta[tid]; }
-        if (d & 2u) pool.L[i] = s_L[tid];
-        if (d) pool.meta[i] = s_meta[tid];
+        uint32_t a = __reduce_add_sync(0xffffffffu, c_alive), v = __reduce_add_sync(0xffffffffu, c_vertex);
+        uint32_t c = __reduce_add_sync(0xffffffffu, c_scatter), pr = __reduce_add_sync(0xffffffffu, c_primary);
+        if (lane == 0) { atomicAdd(&s_stats[0], pr); atomicAdd(&s_stats[2], c); atomicAdd(&s_stats[3], v); atomicAdd(&s_stats[4], a); }
     }
+    __syncthreads();
     if (tid == 0) {
-        if (b_alive > b_dead) atomicAdd((unsigned long long*)(counters + C_ALIVE_BASE + iter_in_batch), (unsigned long long)(b_alive - b_dead));
+        if (s_stats[4]) atomicAdd((unsigned long long*)(counters + C_ALIVE_BASE + iter_in_batch * C_STRIDE), (unsigned long long)s_stats[4]);
+        pool.block_next[blockIdx.x] = s_next;
+        pool.seg_count[blockIdx.x] = s_shadow;
         uint4 st = pool.block_stats[blockIdx.x];
-        st.x += b_primary; st.y += cs.total; st.z += b_scatter; st.w += b_vertex;
+        st.x += s_stats[0]; st.y += s_shadow; st.z += s_stats[2]; st.w += s_stats[3];
         pool.block_stats[blockIdx.x] = st;
     }
 }
@@ -647,8 +681,8 @@ int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_cam
 
 static int ensure_pool(pt_context* ctx, uint32_t P, Pool& pool) {
     uint32_t nblocks = (P + kBlock - 1) / kBlock;
-    size_t per_slot = 16 * 7 + 8 + 8;   // 7 float4 arrays + hit (uint2) + meta (uint2)
-    size_t bytes = per_slot * (size_t)P + 64 * (size_t)nblocks + 256 * 16;
+    size_t per_slot = 16 * 6 + 8 + 8;   // 6 float4 arrays + hit (uint2) + meta (uint2)
+    size_t bytes = per_slot * (size_t)P + 128 * (size_t)nblocks + 256 * 16;
     if (bytes > ctx->pool_bytes) {
         if (ctx->pool_mem) cudaFree(ctx->pool_mem);
         ctx->pool_mem = nullptr; ctx->pool_bytes = 0;
@@ -659,11 +693,13 @@ static int ensure_pool(pt_context* ctx, uint32_t P, Pool& pool) {
     auto take = [&](size_t n) { char* r = p; p += (n + 255) & ~size_t(255); return r; };
     pool.P = P;
     pool.ray_o = (float4*)take(16 * (size_t)P); pool.ray_d = (float4*)take(16 * (size_t)P);
-    pool.beta = (float4*)take(16 * (size_t)P); pool.L = (float4*)take(16 * (size_t)P);
+    pool.beta = (float4*)take(16 * (size_t)P);
     pool.sh_o = (float4*)take(16 * (size_t)P); pool.sh_d = (float4*)take(16 * (size_t)P); pool.sh_c = (float4*)take(16 * (size_t)P);
     pool.meta = (uint2*)take(8 * (size_t)P);
     pool.hit = (uint2*)take(8 * (size_t)P);
     pool.block_stats = (uint4*)take(16 * (size_t)nblocks * 4);
+    pool.seg_count = (uint32_t*)take(4 * (size_t)nblocks * 4);
+    pool.block_next = (unsigned long long*)take(8 * (size_t)nblocks * 4);
     return PT_OK;
 }
 
@@ -676,9 +712,10 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     uint64_t launches = 0, iters = 0;
     if (f.total_work == 0) { if (stats) { stats->samples = 0; } return PT_OK; }
 
-    uint32_t P = rl.prm.path_pool ? rl.prm.path_pool : (1u << 20);
+    // default pool: 4 full waves of shade CTAs (SMs x resident CTAs x slots per CTA), i.e. 2.4 M paths on a 148-SM B200
+    uint32_t P = rl.prm.path_pool ? rl.prm.path_pool : (uint32_t)ctx->sm_count * kShadeMinBlocks * kShadeSlots * 4u;
     if ((uint64_t)P > f.total_work) P = (uint32_t)f.total_work;
-    P = (P + kBlock - 1) / kBlock * kBlock;
+    P = (P + kShadeSlots - 1) / kShadeSlots * kShadeSlots;
     Pool pool;
     int rc = ensure_pool(ctx, P, pool);
     if (rc) return rc;
@@ -690,10 +727,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #define SETS(S, B) { rc = set_smem(ctx, k_trace_closest<S, B>, mode.smem_bytes); if (rc) return rc; rc = set_smem(ctx, k_trace_shadow<S, B>, mode.smem_bytes); if (rc) return rc; }
     PT_DISPATCH(mode, SETS);
 #undef SETS
-    uint64_t first = (uint64_t)P < f.total_work ? (uint64_t)P : f.total_work;
-    PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->d_counters + C_WORK_NEXT, &first, 8, cudaMemcpyHostToDevice, st));
-    const uint32_t sgrid = P / kShadeBlock;
-    PT_CUDA_CHECK(ctx, cudaMemsetAsync(pool.block_stats, 0, 16 * (size_t)sgrid, st));
+    const uint32_t sgrid = P / kShadeSlots;
+    f.chunk = (f.total_work + sgrid - 1) / sgrid;
     const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
     float ms_k[PT_K_COUNT] = {0, 0, 0, 0};
     uint32_t n_k[PT_K_COUNT] = {0, 0, 0, 0};
@@ -712,7 +747,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         ev_class.clear(); ev_used = 0;
     };
     prof_begin(PT_K_GENERATE);
-    k_generate<<<grid, kBlock, 0, st>>>(pool, f, 0ull); launches++;
+    k_generate<<<grid, kBlock, 0, st>>>(pool, f); launches++;
     prof_end();
     const bool mis = rl.prm.strategy == PT_STRATEGY_MIS && scene.n_lights > 0;
     bool done = false;
@@ -725,12 +760,12 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
             prof_end();
 #undef TRACE
             prof_begin(PT_K_SHADE);
-            k_shade<<<P / kShadeBlock, kShadeBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
+            k_shade<<<sgrid, kShadeBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
             prof_end();
             launches += 2;
             if (mis) {
                 prof_begin(PT_K_TRACE_SHADOW);
-#define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, ctx->d_counters + C_SHADOW_BASE + it)
+#define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
                 PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
                 prof_end();
@@ -741,7 +776,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 8 * C_TOTAL, cudaMemcpyDeviceToHost, st));
         PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
         prof_collect();
-        done = ctx->h_counters[C_ALIVE_BASE + kItersPerBatch - 1] == 0;
+        done = ctx->h_counters[C_ALIVE_BASE + (kItersPerBatch - 1) * C_STRIDE] == 0;
     }
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     if (stats) {
@@ -750,7 +785,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         uint64_t a = 0, b = 0, c = 0, d = 0;
         for (auto& v : bs) { a += v.x; b += v.y; c += v.z; d += v.w; }
         stats->samples = f.total_work;
-        stats->rays_primary = a + first; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
+        stats->rays_primary = a; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
         stats->wavefront_iters = iters; stats->kernel_launches = launches; stats->path_pool = P;
         for (int k = 0; k < PT_K_COUNT; ++k) { stats->ms_kernel[k] = ms_k[k]; stats->n_kernel[k] = n_k[k]; }
     }
