@@ -62,8 +62,12 @@ typedef struct {
     uint32_t path_pool;      /* wavefront pool size in paths; 0 = default */
     uint32_t flags;          /* PT_FLAG_* */
 } pt_render_params;
-enum { PT_FLAG_PROFILE = 1 /* time every kernel launch with CUDA events into pt_stats.ms_kernel (slower) */ };
-enum { PT_K_GENERATE = 0, PT_K_TRACE_CLOSEST = 1, PT_K_SHADE = 2, PT_K_TRACE_SHADOW = 3, PT_K_COUNT = 4 };
+enum {
+    PT_FLAG_PROFILE = 1,    /* time every kernel launch with CUDA events into pt_stats.ms_kernel (slower) */
+    PT_FLAG_HBM_QUEUES = 2  /* force the HBM-queue wavefront (one launch per stage per bounce) even when the scene is small
+                               enough for the shared-memory wavefront (one persistent launch per frame) */
+};
+enum { PT_K_GENERATE = 0, PT_K_TRACE_CLOSEST = 1, PT_K_SHADE = 2, PT_K_TRACE_SHADOW = 3, PT_K_SMEM_WAVEFRONT = 4, PT_K_COUNT = 5 };
 
 typedef struct {
     uint64_t samples;           /* camera samples started */
@@ -73,9 +77,10 @@ typedef struct {
     uint64_t kernel_launches;   /* kernels launched by this call */
     float ms_total;             /* device time of the call, CUDA events */
     float ms_upload, ms_render, ms_download;
-    float ms_kernel[4];         /* PT_FLAG_PROFILE only: summed CUDA-event time per kernel class (PT_K_*) */
-    uint32_t n_kernel[4];       /* launches per kernel class */
+    float ms_kernel[5];         /* PT_FLAG_PROFILE only: summed CUDA-event time per kernel class (PT_K_*) */
+    uint32_t n_kernel[5];       /* launches per kernel class */
     uint32_t path_pool;         /* pool size actually used */
+    float phase_share[3];       /* PT_FLAG_PROFILE, shared-memory wavefront: share of CTA cycles in closest-hit+sort, shade, shadow */
 } pt_stats;
 
 typedef struct pt_context pt_context;

@@ -37,16 +37,18 @@ class pt_stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_scattered", C.c_uint64),
                 ("path_vertices", C.c_uint64), ("wavefront_iters", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("ms_total", C.c_float), ("ms_upload", C.c_float), ("ms_render", C.c_float), ("ms_download", C.c_float),
-                ("ms_kernel", C.c_float * 4), ("n_kernel", C.c_uint32 * 4), ("path_pool", C.c_uint32)]
+                ("ms_kernel", C.c_float * 5), ("n_kernel", C.c_uint32 * 5), ("path_pool", C.c_uint32),
+                ("phase_share", C.c_float * 3)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_}
         d["ms_kernel"] = dict(zip(KERNEL_CLASSES, list(self.ms_kernel)))
         d["n_kernel"] = dict(zip(KERNEL_CLASSES, list(self.n_kernel)))
+        d["phase_share"] = dict(zip(("closest_hit", "shade", "shadow"), list(self.phase_share)))
         return d
 
 
-KERNEL_CLASSES = ("generate", "trace_closest", "shade", "trace_shadow")
+KERNEL_CLASSES = ("generate", "trace_closest", "shade", "trace_shadow", "smem_wavefront")
 
 
 STRATEGY = {"mis": 0, "brdf_only": 1}
@@ -99,10 +101,11 @@ def camera_struct(cam: Camera) -> pt_camera:
 
 
 def render_params(spp=3000, sample_offset=0, min_depth=4, max_depth=50, strategy="mis", traversal="auto", seed=0x5EED,
-                  t_min=1e-3, path_pool=0, profile=False) -> pt_render_params:
+                  t_min=1e-3, path_pool=0, profile=False, hbm_queues=False) -> pt_render_params:
     s = STRATEGY[strategy] if isinstance(strategy, str) else int(strategy)
     t = TRAVERSAL[traversal] if isinstance(traversal, str) else int(traversal)
-    return pt_render_params(spp, sample_offset, min_depth, max_depth, s, t, seed, t_min, path_pool, 1 if profile else 0)
+    return pt_render_params(spp, sample_offset, min_depth, max_depth, s, t, seed, t_min, path_pool,
+                            (1 if profile else 0) | (2 if hbm_queues else 0))
 
 
 class Context:

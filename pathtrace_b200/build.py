@@ -13,8 +13,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIBDIR = os.path.join(_HERE, "lib")
 LIB = os.environ.get("PT_LIB") or os.path.join(LIBDIR, "libpathtrace_b200.so")   # PT_LIB: development override (kernel variants)
-SOURCES = ["capi.cu", "lbvh.cu", "wavefront.cu"]
-HEADERS = ["pt_internal.h", "pt_math.cuh", "pt_shade.cuh", os.path.join("..", "..", "include", "pathtrace_b200.h")]
+SOURCES = ["capi.cu", "lbvh.cu", "wavefront.cu", "smem_wavefront.cu"]
+HEADERS = ["pt_internal.h", "pt_math.cuh", "pt_shade.cuh", "pt_wave.cuh", os.path.join("..", "..", "include", "pathtrace_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "-ccbin", "g++"]
 

@@ -1,0 +1,319 @@
+// pt_wave.cuh — device code shared by the two wavefront formulations (HBM queues: wavefront.cu; shared-memory queues:
+// smem_wavefront.cu): frame / scene views, primary-ray generation, LBVH traversal, and the per-vertex shading step.
+// Citations are into /root/reference/src.
+#pragma once
+#include <cfloat>
+
+#include "pt_internal.h"
+#include "pt_shade.cuh"
+
+namespace ptw {
+using namespace ptd;
+
+constexpr int kStackDepth = 64;
+constexpr uint32_t kMaxSmemPrims = 1024;   // scene staged in shared memory up to this many objects
+
+struct Frame {
+    CameraDev cam;
+    uint32_t npix;
+    uint64_t total_work;     // npix * spp of this call
+    uint64_t chunk;          // work items owned by each shade-CTA (contiguous range)
+    uint32_t sample_offset, min_depth, max_depth, strategy;
+    uint32_t k0, k1;         // Philox key
+    float t_min;
+    float4* accum;           // per pixel: sum r, g, b, (reserved)
+};
+
+struct SceneView {
+    const float4* prims;
+    const float4* mats;
+    const uint32_t* light_ids;
+    const float4* nodes;
+    uint32_t n_objects, n_lights, n_nodes;
+};
+
+PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
+    uint32_t sample = f.sample_offset + (uint32_t)(w / f.npix);
+    uint32_t pixel = (uint32_t)(w % f.npix);
+    uint32_t x = pixel % f.cam.width, y = pixel / f.cam.width;
+    uint4 r = philox4x32_10(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, u01(r.x), u01(r.y));   // world.rs:299
+    ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
+    rd = make_float4(d.x, d.y, d.z, 0.0f);
+    meta = make_uint2(pixel | 0x80000000u, sample & 0x00ffffffu);
+}
+
+// ------------------------------------------------------------------------------------ traversal
+// Scene staged in shared memory: [nodes: 4 float4 each][prims: 3 float4 each (q0,q1,q2)]
+template <bool SMEM, int PS = 3>
+struct Geo {
+    const float4* nodes;
+    const float4* prims;   // stride PS (smem: 3 = q0,q1,q2 only; 4 = with the normal) or 4 (global)
+    PT_DEV void node(int i, float4& a, float4& b, float4& c, float4& d) const {
+        if (SMEM) { a = nodes[4 * i]; b = nodes[4 * i + 1]; c = nodes[4 * i + 2]; d = nodes[4 * i + 3]; }
+        else { a = __ldg(nodes + 4 * i); b = __ldg(nodes + 4 * i + 1); c = __ldg(nodes + 4 * i + 2); d = __ldg(nodes + 4 * i + 3); }
+    }
+    PT_DEV void prim(int i, float4& q0, float4& q1, float4& q2) const {
+        if (SMEM) { q0 = prims[PS * i]; q1 = prims[PS * i + 1]; q2 = prims[PS * i + 2]; }
+        else { q0 = __ldg(prims + 4 * (size_t)i); q1 = __ldg(prims + 4 * (size_t)i + 1); q2 = __ldg(prims + 4 * (size_t)i + 2); }
+    }
+};
+template <bool SMEM>
+PT_DEV Geo<SMEM> stage_scene(const SceneView& s, float4* smem, bool want_nodes) {
+    Geo<SMEM> g;
+    if (SMEM) {
+        uint32_t nn = want_nodes ? s.n_nodes * 4 : 0;
+        for (uint32_t i = threadIdx.x; i < nn; i += blockDim.x) smem[i] = __ldg(s.nodes + i);
+        for (uint32_t i = threadIdx.x; i < s.n_objects * 3; i += blockDim.x) smem[nn + i] = __ldg(s.prims + 4 * (i / 3) + (i % 3));
+        __syncthreads();
+        g.nodes = smem; g.prims = smem + nn;
+    } else {
+        g.nodes = s.nodes; g.prims = s.prims;
+    }
+    return g;
+}
+
+// Slab test against [lo,hi]; conservative: NaN slabs (0 * inf) are ignored, far side widened by 2 ulp.
+PT_DEV bool slab(float3 lo, float3 hi, float3 ro, float3 inv, float t_min, float t_max, float& tnear) {
+    float tx0 = (lo.x - ro.x) * inv.x, tx1 = (hi.x - ro.x) * inv.x;
+    float ty0 = (lo.y - ro.y) * inv.y, ty1 = (hi.y - ro.y) * inv.y;
+    float tz0 = (lo.z - ro.z) * inv.z, tz1 = (hi.z - ro.z) * inv.z;
+    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), t_min));
+    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), t_max));
+    tnear = tn;
+    return tn <= tf * 1.0000004f;
+}
+
+// Closest hit.  Winner = smallest t in [t_min, inf); equal t -> higher object index (world.rs:281-287 scans
+// in index order with an inclusive t_max, so a later object replaces an earlier one on a tie).
+template <bool SMEM, bool BRUTE, class G>
+PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
+    best_t = FLT_MAX; best_id = -1;
+    float tmax = __int_as_float(0x7f800000);
+    auto test = [&](int id) {
+        float4 q0, q1, q2;
+        g.prim(id, q0, q1, q2);
+        float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
+        if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
+    };
+    if (BRUTE) {
+        for (int id = 0; id < (int)n_objects; ++id) test(id);
+    } else {
+        float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
+        int stack[kStackDepth];
+        int sp = 0, node = 0;
+        while (true) {
+            float4 a, b, c, d;
+            g.node(node, a, b, c, d);
+            int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
+            float tl, tr;
+            bool hl = slab(v3(a), v3(b), ro, inv, t_min, tmax, tl);
+            bool hr = slab(v3(c), v3(d), ro, inv, t_min, tmax, tr);
+            if (hl && cl < 0) { test(~cl); hl = false; }
+            if (hr && cr < 0) { test(~cr); hr = false; }
+            if (hl && hr) {
+                if (tr < tl) { int t = cl; cl = cr; cr = t; }
+                stack[sp++] = cr; node = cl;
+            } else if (hl) node = cl;
+            else if (hr) node = cr;
+            else { if (sp == 0) break; node = stack[--sp]; }
+        }
+    }
+    if (best_id >= 0) best_t = tmax;
+}
+// Any hit in [t_min, t_max] (rendering.rs:62-65)
+template <bool SMEM, bool BRUTE, class G>
+PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float t_max) {
+    if (BRUTE) {
+        bool occluded = false;
+        for (int id = 0; id < (int)n_objects; ++id) {
+            float4 q0, q1, q2;
+            g.prim(id, q0, q1, q2);
+            occluded |= hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f;
+        }
+        return occluded;
+    }
+    float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
+    int stack[kStackDepth];
+    int sp = 0, node = 0;
+    while (true) {
+        float4 a, b, c, d;
+        g.node(node, a, b, c, d);
+        int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
+        float tl, tr;
+        bool hl = slab(v3(a), v3(b), ro, inv, t_min, t_max, tl);
+        bool hr = slab(v3(c), v3(d), ro, inv, t_min, t_max, tr);
+        if (hl && cl < 0) {
+            float4 q0, q1, q2; g.prim(~cl, q0, q1, q2);
+            if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
+            hl = false;
+        }
+        if (hr && cr < 0) {
+            float4 q0, q1, q2; g.prim(~cr, q0, q1, q2);
+            if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
+            hr = false;
+        }
+        if (hl && hr) { stack[sp++] = cr; node = cl; }
+        else if (hl) node = cl;
+        else if (hr) node = cr;
+        else { if (sp == 0) return false; node = stack[--sp]; }
+    }
+}
+
+// rendering.rs:91-98
+PT_DEV float rr_prob(const Frame& f, float3 tn, uint32_t depth) {
+    if (depth < f.min_depth) return 1.0f;
+    float l = fminf(luminance(tn), 1.0f);
+    if (depth >= f.max_depth) l *= exp2f(-(float)(depth - f.min_depth));
+    return l;
+}
+
+// meta packing: x = pixel | alive << 31, y = sample | depth << 24
+PT_DEV uint2 pack_meta(uint32_t pixel, uint32_t sample, uint32_t depth, bool alive) {
+    return make_uint2(pixel | (alive ? 0x80000000u : 0u), (sample & 0x00ffffffu) | (depth << 24));
+}
+#define META_ALIVE(m) (((m).x >> 31) != 0u)
+#define META_PIXEL(m) ((m).x & 0x7fffffffu)
+#define META_SAMPLE(m) ((m).y & 0x00ffffffu)
+#define META_DEPTH(m) ((m).y >> 24)
+
+enum { CLS_MIRROR = 0, CLS_DIFFUSE = 1, CLS_EMISSIVE = 2, CLS_MISS = 3, CLS_DEAD = 4, CLS_COUNT = 5 };
+
+
+// ------------------------------------------------------------------------------------ scene access for shading
+// Global-memory view (HBM-queue wavefront): 4 float4 per primitive, 2 float4 per material, through the read-only path.
+struct SceneGlobal {
+    const float4* prims; const float4* mats; const uint32_t* light_ids; uint32_t n_lights;
+    PT_DEV void prim(int i, float4& q0, float4& q1, float4& q2, float4& q3) const {
+        q0 = __ldg(prims + 4 * (size_t)i); q1 = __ldg(prims + 4 * (size_t)i + 1); q2 = __ldg(prims + 4 * (size_t)i + 2); q3 = __ldg(prims + 4 * (size_t)i + 3);
+    }
+    PT_DEV Mat mat(int i) const { return load_mat(mats, i); }
+    PT_DEV float3 emission(int i) const { return v3(__ldg(mats + 2 * (size_t)i)); }
+    PT_DEV uint32_t light(uint32_t k) const { return __ldg(light_ids + k); }
+};
+// Shared-memory view (smem wavefront): same records staged once per CTA.
+struct SceneShared {
+    const float4* prims; const float4* mats; const uint32_t* light_ids; uint32_t n_lights;
+    PT_DEV void prim(int i, float4& q0, float4& q1, float4& q2, float4& q3) const {
+        q0 = prims[4 * i]; q1 = prims[4 * i + 1]; q2 = prims[4 * i + 2]; q3 = prims[4 * i + 3];
+    }
+    PT_DEV Mat mat(int i) const {
+        float4 m0 = mats[2 * i], m1 = mats[2 * i + 1];
+        Mat m; m.color = v3(m0); m.kind = __float_as_uint(m0.w); m.roughness = m1.x; m.metallic = m1.y; m.ior = m1.z;
+        return m;
+    }
+    PT_DEV float3 emission(int i) const { return v3(mats[2 * i]); }
+    PT_DEV uint32_t light(uint32_t k) const { return light_ids[k]; }
+};
+
+// ------------------------------------------------------------------------------------ one path vertex
+// rendering.rs:34-142 in the iterative form of SURVEY A.6, for ONE live slot whose closest hit is known.
+// Outcome: either the path ends (finished; add_L says whether Ladd goes to the pixel), or it continues with a new
+// ray / throughput / meta and possibly a shadow ray (emit_shadow) whose contribution sh_c is added when unoccluded.
+struct VertexOut {
+    bool finished, add_L, emit_shadow, vertex;
+    float3 Ladd;
+    float3 sh_d, sh_c; float sh_tmax;          // shadow ray from p (== new_ro.xyz) toward the light sample
+    float4 new_ro, new_rd; float3 new_beta; uint2 new_meta;
+};
+template <class Scene>
+PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 ro4, float4 rd4, float3 beta, uint2 h, uint2 meta) {
+    VertexOut o;
+    o.finished = false; o.add_L = false; o.emit_shadow = false; o.vertex = false;
+    o.Ladd = v3(0.f, 0.f, 0.f); o.sh_d = v3(0.f, 0.f, 0.f); o.sh_c = v3(0.f, 0.f, 0.f); o.sh_tmax = 0.f;
+    o.new_ro = ro4; o.new_rd = rd4; o.new_beta = beta; o.new_meta = meta;
+    const uint32_t depth = META_DEPTH(meta);
+    if (h.y == 0xffffffffu) { o.finished = true; return o; }   // background is black, rendering.rs:140-141
+    const float3 ro = v3(ro4), rd = v3(rd4);
+    const int obj = (int)h.y;
+    const float t = __uint_as_float(h.x);
+    float4 q0, q1, q2, q3;
+    sc.prim(obj, q0, q1, q2, q3);
+    Mat m = sc.mat(obj);
+    float3 p = ro + rd * t;
+    const bool is_tri = __float_as_uint(q0.w) == PT_KIND_TRIANGLE;
+    float3 n_out = is_tri ? v3(q3) : (p - v3(q0)) / q1.x;     // shape.rs:195 / :86
+    const bool front = dot(rd, n_out) < 0.0f;                 // base.rs:20
+    float3 n = front ? n_out : -n_out;
+    if (m.kind == PT_MATK_EMISSIVE && dot(m.color, m.color) > 0.0f) {
+        // rendering.rs:42-49 for a primary ray; :106-121 (look-ahead MIS) for a scattered ray
+        float3 L;
+        if (depth == 0) L = m.color;
+        else if (!mis) L = beta * m.color;                    // rendering.rs:226-228
+        else {
+            float ps;                                         // shape pdf from the previous vertex, NOT / n_lights (Q2)
+            if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), ro, p, ld, dd); }
+            else ps = sphere_pdf_omega(v3(q0), q1.x, ro);
+            float pb = rd4.w;
+            L = beta * (m.color * (pb / (pb + ps)));
+        }
+        o.finished = true; o.add_L = true; o.Ladd = L;
+        return o;
+    }
+    o.vertex = true;
+    const uint32_t pixel = META_PIXEL(meta), sample = META_SAMPLE(meta);
+    uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
+    uint4 b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
+    // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by the shadow stage
+    bool want_shadow = false;
+    if (mis && sc.n_lights > 0) {
+        uint32_t li = sc.light(urange(b0.x, sc.n_lights));
+        float4 l0, l1, l2, l3;
+        sc.prim((int)li, l0, l1, l2, l3);
+        float3 le = sc.emission((int)li);
+        float3 ldir; float dist, pdf_shape;
+        sample_light_shape(l0, l1, l2, l3, p, u01(b0.y), u01(b0.z), ldir, dist, pdf_shape);
+        float pl = pdf_shape / (float)sc.n_lights;        // world.rs:260
+        float cos_theta = fabsf(dot(n, ldir));            // rendering.rs:68
+        float3 fe; float pb;
+        bsdf_eval(m, rd, ro4.w, ldir, n, fe, pb);         // inherited eta_ratio (Q3)
+        float w_nee = pl / (pl + pb);
+        float3 c = beta * fe * le * (w_nee * cos_theta / pl);
+        if (finite3(c) && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
+            want_shadow = true;
+            o.sh_d = ldir; o.sh_c = c; o.sh_tmax = dist - 0.001f;   // rendering.rs:64
+        }
+    }
+    // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
+    float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
+    float3 wo, fs; float pdf, cos_s;
+    bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.w), u01(b1.x), u01(b1.y), wo, fs, pdf, cos_s);
+    float3 tn = beta * fs * (cos_s / pdf);
+    ok = ok && finite3(tn);
+    float q = ok ? rr_prob(f, tn, depth) : 0.0f;
+    if (!ok || u01(b1.z) > q) {
+        o.finished = true;                                  // D of this vertex is dropped too (Q1)
+        return o;
+    }
+    o.emit_shadow = want_shadow;
+    o.new_beta = tn / q;
+    o.new_ro = make_float4(p.x, p.y, p.z, eta_new);         // rendering.rs:86-87
+    o.new_rd = make_float4(wo.x, wo.y, wo.z, pdf);
+    o.new_meta = pack_meta(pixel, sample, depth + 1, true);
+    return o;
+}
+
+// ------------------------------------------------------------------------------------ host helpers
+inline SceneView make_scene_view(const SceneDev& d) {
+    SceneView v;
+    v.prims = d.prims; v.mats = d.mats; v.light_ids = d.light_ids; v.nodes = d.nodes;
+    v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
+    return v;
+}
+inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {
+    Frame f;
+    f.cam.origin = make_float3(c.origin[0], c.origin[1], c.origin[2]);
+    f.cam.llc = make_float3(c.lower_left_corner[0], c.lower_left_corner[1], c.lower_left_corner[2]);
+    f.cam.horizontal = make_float3(c.horizontal[0], c.horizontal[1], c.horizontal[2]);
+    f.cam.vertical = make_float3(c.vertical[0], c.vertical[1], c.vertical[2]);
+    f.cam.width = c.width; f.cam.height = c.height;
+    f.npix = c.width * c.height;
+    f.total_work = (uint64_t)f.npix * p.spp;
+    f.sample_offset = p.sample_offset; f.min_depth = p.min_depth; f.max_depth = p.max_depth; f.strategy = p.strategy;
+    f.k0 = (uint32_t)p.seed; f.k1 = (uint32_t)(p.seed >> 32);
+    f.t_min = p.t_min;
+    f.accum = accum;
+    return f;
+}
+
+}  // namespace ptw

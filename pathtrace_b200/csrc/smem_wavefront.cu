@@ -1,0 +1,338 @@
+// smem_wavefront.cu — the wavefront sample loop with its queues in SHARED memory (sm_100a, 227 KB per SM).
+//
+// Same stages as wavefront.cu (K1 generate, K3 closest hit, K4/K6/K7 shade, K5 shadow, K8 accumulate), same device
+// functions (pt_wave.cuh), same counter-based RNG — but when the whole scene (primitives, materials, LBVH) fits in a few
+// KB of shared memory, nothing about a path needs to leave the SM between bounces.  Each CTA owns kSwSlots path slots
+// whose SoA float4 queues (ray origin|eta, direction|pdf, throughput, hit, meta, shadow queue) live in shared memory,
+// owns a contiguous range of the (pixel, sample) work list, and runs the wavefront to completion on its own:
+//
+//   loop:  T  closest hit of every live slot, slot order (coherent straight-line code)      world.rs:270-290
+//          S  counting sort of the slots by hit class (mirror / diffuse / emissive / miss)  warp ballot + popc
+//          A  warps pull 32-slot tiles of the sorted list: shade_vertex(), shadow-queue compaction (ballot/popc + one
+//             shared atomic per warp), accumulate finished paths, re-seed their slots       rendering.rs:34-142
+//          H  any-hit over the compacted shadow queue, accumulate unoccluded contributions  rendering.rs:62-65
+//
+// HBM traffic is what the algorithm needs: one float4 atomic add per finished path / unoccluded shadow ray.
+// CTAs never communicate, so one launch renders the frame: no per-bounce launches, no host round trips.
+#include <cstdio>
+#include <vector>
+
+#include "pt_wave.cuh"
+
+using namespace ptw;
+
+namespace {
+
+#ifndef PT_SW_BLOCK
+#define PT_SW_BLOCK 256
+#endif
+#ifndef PT_SW_SPT
+#define PT_SW_SPT 2
+#endif
+#ifndef PT_SW_MIN_BLOCKS
+#define PT_SW_MIN_BLOCKS 4
+#endif
+constexpr int kSwBlock = PT_SW_BLOCK, kSwSpt = PT_SW_SPT, kSwSlots = kSwBlock * kSwSpt, kSwMinBlocks = PT_SW_MIN_BLOCKS;
+
+struct SwOut {
+    uint4* block_stats;       // per CTA: primary, shadow, scattered, vertices
+    uint32_t* block_iters;    // per CTA: wavefront iterations it ran
+    unsigned long long* block_clk;   // per CTA (PROF only): cycles in phases T+S, A, H
+};
+
+// Bytes of dynamic shared memory for a scene (must match the carve-up in the kernel).
+size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bool brute) {
+    size_t b = 0;
+    b += 16 * (size_t)kSwSlots * 5;                 // ro, rd, beta, shadow d, shadow c
+    b += 8 * (size_t)kSwSlots * 2;                  // hit, meta
+    b += 16 * ((brute ? 0 : (size_t)n_nodes * 4) + (size_t)n_objects * 4 + (size_t)n_objects * 2);
+    b += 4 * (((size_t)n_lights + 3) & ~size_t(3));
+    b += 2 * (size_t)kSwSlots;                      // sorted order
+    return b;
+}
+
+template <bool BRUTE, bool PROF>
+__global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out) {
+    constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NTILES = kSwSlots / 32;
+    extern __shared__ float4 smem[];
+    float4* s_ro = smem;
+    float4* s_rd = s_ro + kSwSlots;
+    float4* s_beta = s_rd + kSwSlots;
+    float4* s_shd = s_beta + kSwSlots;                 // shadow queue: direction.xyz, t_max
+    float4* s_shc = s_shd + kSwSlots;                  // contribution.rgb, slot bits
+    uint2* s_hit = reinterpret_cast<uint2*>(s_shc + kSwSlots);
+    uint2* s_meta = s_hit + kSwSlots;
+    float4* s_nodes = reinterpret_cast<float4*>(s_meta + kSwSlots);
+    float4* s_prims = s_nodes + (BRUTE ? 0 : s.n_nodes * 4);
+    float4* s_mats = s_prims + s.n_objects * 4;
+    uint32_t* s_lights = reinterpret_cast<uint32_t*>(s_mats + s.n_objects * 2);
+    uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));
+    __shared__ uint16_t s_cls_cnt[CLS_COUNT][SPT * NW];
+    __shared__ unsigned long long s_next;      // this CTA's next work item
+    __shared__ uint32_t s_shadow, s_tile, s_alive;
+    __shared__ unsigned long long s_clk[4];    // PROF: t_prev, T+S, A, H
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool mis = f.strategy == PT_STRATEGY_MIS;
+    const uint64_t work_lo = (uint64_t)blockIdx.x * f.chunk, work_hi = work_lo + f.chunk < f.total_work ? work_lo + f.chunk : f.total_work;
+
+    // ---- stage the scene once
+    if (!BRUTE) for (uint32_t i = tid; i < s.n_nodes * 4; i += kSwBlock) s_nodes[i] = __ldg(s.nodes + i);
+    for (uint32_t i = tid; i < s.n_objects * 4; i += kSwBlock) s_prims[i] = __ldg(s.prims + i);
+    for (uint32_t i = tid; i < s.n_objects * 2; i += kSwBlock) s_mats[i] = __ldg(s.mats + i);
+    for (uint32_t i = tid; i < s.n_lights; i += kSwBlock) s_lights[i] = __ldg(s.light_ids + i);
+    Geo<true, 4> g; g.nodes = s_nodes; g.prims = s_prims;
+    const SceneShared sc{s_prims, s_mats, s_lights, s.n_lights};
+
+    // ---- K1: initial fill of this CTA's slots from its work range
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+        uint32_t j = k * kSwBlock + tid;
+        uint64_t w = work_lo + j;
+        if (w < work_hi) {
+            float4 ro, rd; uint2 m;
+            make_primary(f, w, ro, rd, m);
+            s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
+        } else {
+            s_meta[j] = make_uint2(0u, 0u);
+        }
+    }
+    if (tid == 0) {
+        s_next = work_lo + kSwSlots;
+        if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = s_clk[3] = 0; }
+    }
+    uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // meaningful on lane 0 of each warp / tid 0
+    __syncthreads();
+
+    while (true) {
+        // ---- phase T: closest hit in slot order + classification
+        uint32_t cls[SPT], rank[SPT];
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            uint32_t j = k * kSwBlock + tid;
+            uint2 m = s_meta[j];
+            uint32_t c = CLS_DEAD;
+            if (META_ALIVE(m)) {
+                float4 ro = s_ro[j], rd = s_rd[j];
+                float t; int id;
+                closest_hit<true, BRUTE>(g, s.n_objects, v3(ro), v3(rd), f.t_min, t, id);
+                s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
+                if (id < 0) c = CLS_MISS;
+                else {
+                    uint32_t kind = __float_as_uint(s_mats[2 * id].w);
+                    c = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
+                }
+            }
+            cls[k] = c; rank[k] = 0;
+#pragma unroll
+            for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) {
+                uint32_t b = __ballot_sync(0xffffffffu, c == cc);
+                if (lane == 0) s_cls_cnt[cc][k * NW + warp] = (uint16_t)__popc(b);
+                if (c == cc) rank[k] = __popc(b & ((1u << lane) - 1));
+            }
+        }
+        if (tid == 0) { s_shadow = 0; s_tile = 0; s_alive = 0; }
+        __syncthreads();
+        // ---- phase S: exclusive prefix over the CLS_COUNT x (SPT*NW) counts in (class, group) order, one warp
+        if (tid < 32) {
+            constexpr uint32_t N = CLS_COUNT * SPT * NW;
+            uint16_t* flat = &s_cls_cnt[0][0];
+            uint32_t run = 0;
+            for (uint32_t k0 = 0; k0 < N; k0 += 32) {
+                uint32_t k = k0 + tid;
+                uint32_t v = k < N ? flat[k] : 0, x = v;
+                for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+                if (k < N) flat[k] = (uint16_t)(run + x - v);
+                run += __shfl_sync(0xffffffffu, x, 31);
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) s_order[s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)(k * kSwBlock + tid);
+        __syncthreads();
+        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[1] += t - s_clk[0]; s_clk[0] = t; }
+
+        // ---- phase A: dynamic tiles of the class-sorted slot list
+        while (true) {
+            uint32_t tile = 0;
+            if (lane == 0) tile = atomicAdd(&s_tile, 1u);
+            tile = __shfl_sync(0xffffffffu, tile, 0);
+            if (tile >= NTILES) break;
+            const uint32_t j = s_order[tile * 32 + lane];
+            const uint2 meta = s_meta[j];
+            bool alive = META_ALIVE(meta);
+            if (!__any_sync(0xffffffffu, alive)) break;          // sorted: dead slots are last
+            bool finished = false, emit_shadow = false, add_L = false, vertex = false;
+            float3 Ladd = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
+            float sh_tmax = 0.f;
+            if (alive) {
+                VertexOut vo = shade_vertex(sc, f, mis, s_ro[j], s_rd[j], v3(s_beta[j]), s_hit[j], meta);
+                finished = vo.finished; add_L = vo.add_L; Ladd = vo.Ladd; vertex = vo.vertex;
+                if (!vo.finished) {
+                    emit_shadow = vo.emit_shadow; sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
+                    s_ro[j] = vo.new_ro; s_rd[j] = vo.new_rd; s_meta[j] = vo.new_meta;
+                    s_beta[j] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
+                }
+            }
+            // shadow queue compaction: warp ballot/popc + one shared-memory atomic per warp.  The ray starts at the new
+            // origin of slot j (the hit point), so an entry is (direction, t_max, contribution, slot).
+            {
+                uint32_t bal = __ballot_sync(0xffffffffu, emit_shadow);
+                uint32_t sbase = 0;
+                if (lane == 0 && bal) sbase = atomicAdd(&s_shadow, (uint32_t)__popc(bal));
+                sbase = __shfl_sync(0xffffffffu, sbase, 0);
+                if (emit_shadow) {
+                    uint32_t e = sbase + __popc(bal & ((1u << lane) - 1));
+                    s_shd[e] = make_float4(sh_d.x, sh_d.y, sh_d.z, sh_tmax);
+                    s_shc[e] = make_float4(sh_c.x, sh_c.y, sh_c.z, __uint_as_float(j));
+                }
+                c_shadow += __popc(bal);
+                c_vertex += __popc(__ballot_sync(0xffffffffu, vertex));
+                c_scatter += __popc(__ballot_sync(0xffffffffu, alive && !finished));
+            }
+            // K8 accumulate (world.rs:296-313) + regeneration from this CTA's private work range
+            {
+                uint32_t bal = __ballot_sync(0xffffffffu, finished);
+                unsigned long long wbase = 0;
+                if (lane == 0 && bal) wbase = atomicAdd(&s_next, (unsigned long long)__popc(bal));
+                wbase = __shfl_sync(0xffffffffu, wbase, 0);
+                if (finished) {
+                    if (add_L) atomicAdd(f.accum + META_PIXEL(meta), make_float4(Ladd.x, Ladd.y, Ladd.z, 0.f));
+                    uint64_t w = wbase + __popc(bal & ((1u << lane) - 1));
+                    if (w < work_hi) {
+                        float4 ro, rd; uint2 m;
+                        make_primary(f, w, ro, rd, m);
+                        s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
+                    } else {
+                        s_meta[j] = make_uint2(0u, 0u);
+                        alive = false;
+                    }
+                }
+                uint32_t na = __popc(__ballot_sync(0xffffffffu, alive));
+                if (lane == 0 && na) atomicAdd(&s_alive, na);
+            }
+        }
+        __syncthreads();
+        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
+        const uint32_t alive_now = s_alive, n_sh = s_shadow;
+
+        // ---- phase H: any-hit over the compacted shadow queue (dense: every warp is full except the last)
+        for (uint32_t e = tid; e < n_sh; e += kSwBlock) {
+            float4 d = s_shd[e], c = s_shc[e];
+            uint32_t j = __float_as_uint(c.w);
+            float4 o = s_ro[j];
+            if (!any_hit<true, BRUTE>(g, s.n_objects, v3(o), v3(d), f.t_min, d.w))
+                atomicAdd(f.accum + META_PIXEL(s_meta[j]), make_float4(c.x, c.y, c.z, 0.f));   // rendering.rs:70-80
+        }
+        ++iters;
+        __syncthreads();
+        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[3] += t - s_clk[0]; s_clk[0] = t; }
+        if (alive_now == 0) break;
+    }
+
+    // ---- bookkeeping: lane 0 of every warp holds its warp's counters
+    __shared__ uint32_t s_stats[3];
+    if (tid < 3) s_stats[tid] = 0;
+    __syncthreads();
+    if (lane == 0) { atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex); }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long handed = s_next < work_hi ? s_next : work_hi;
+        uint32_t primary = work_hi > work_lo ? (uint32_t)(handed - work_lo) : 0u;
+        out.block_stats[blockIdx.x] = make_uint4(primary, s_stats[0], s_stats[1], s_stats[2]);
+        out.block_iters[blockIdx.x] = iters;
+        if (PROF) { out.block_clk[3 * blockIdx.x] = s_clk[1]; out.block_clk[3 * blockIdx.x + 1] = s_clk[2]; out.block_clk[3 * blockIdx.x + 2] = s_clk[3]; }
+    }
+}
+
+}  // namespace
+
+// Whether the shared-memory wavefront applies to this scene: the queues plus the staged scene must leave room for at
+// least three CTAs per SM (occupancy is what hides the barriers between phases).
+bool smem_wavefront_applicable(const pt_context* ctx, const SceneDev& scene, bool brute) {
+    (void)ctx;
+    size_t bytes = sw_smem_bytes(scene.n_objects, scene.n_nodes, scene.n_lights, brute) + 1024;
+    return scene.n_objects > 0 && scene.n_objects <= kMaxSmemPrims && bytes * 3 <= 227 * 1024;
+}
+
+int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, pt_stats* stats) {
+    cudaStream_t st = ctx->stream;
+    const SceneDev& scene = *rl.scene;
+    SceneView sv = make_scene_view(scene);
+    Frame f = make_frame(rl.cam, rl.prm, rl.d_accum);
+    if (f.total_work == 0) { if (stats) stats->samples = 0; return PT_OK; }
+    const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
+    const size_t smem = sw_smem_bytes(scene.n_objects, scene.n_nodes, scene.n_lights, brute);
+
+    auto pick = [&](auto kernel, int& occ) -> int {
+        PT_CUDA_CHECK(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kSwBlock, smem));
+        return PT_OK;
+    };
+    int occ = 0, rc;
+    if (brute) rc = profile ? pick(k_smem_wavefront<true, true>, occ) : pick(k_smem_wavefront<true, false>, occ);
+    else rc = profile ? pick(k_smem_wavefront<false, true>, occ) : pick(k_smem_wavefront<false, false>, occ);
+    if (rc) return rc;
+    if (occ < 1) { ctx->err = "smem wavefront: kernel does not fit on an SM"; return PT_ERR_CUDA; }
+
+    // one resident wave of CTAs by default (persistent: each CTA runs its share of the work list to completion);
+    // path_pool overrides the number of slots, i.e. the number of CTAs
+    uint64_t want = rl.prm.path_pool ? ((uint64_t)rl.prm.path_pool + kSwSlots - 1) / kSwSlots : (uint64_t)ctx->sm_count * occ;
+    uint64_t need = (f.total_work + kSwSlots - 1) / kSwSlots;
+    uint32_t grid = (uint32_t)(want < need ? want : need);
+    if (grid == 0) grid = 1;
+    f.chunk = (f.total_work + grid - 1) / grid;
+
+    size_t out_bytes = (16 + 4 + 24) * (size_t)grid + 1024;
+    if (out_bytes > ctx->pool_bytes) {
+        if (ctx->pool_mem) cudaFree(ctx->pool_mem);
+        ctx->pool_mem = nullptr; ctx->pool_bytes = 0;
+        PT_CUDA_CHECK(ctx, cudaMalloc(&ctx->pool_mem, out_bytes));
+        ctx->pool_bytes = out_bytes;
+    }
+    SwOut out;
+    char* p = static_cast<char*>(ctx->pool_mem);
+    out.block_stats = reinterpret_cast<uint4*>(p);
+    out.block_clk = reinterpret_cast<unsigned long long*>(p + 16 * (size_t)grid);
+    out.block_iters = reinterpret_cast<uint32_t*>(p + (16 + 24) * (size_t)grid);
+
+    if (profile) {
+        while (ctx->prof_events.size() < 2) { cudaEvent_t e; PT_CUDA_CHECK(ctx, cudaEventCreate(&e)); ctx->prof_events.push_back(e); }
+        PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[0], st));
+    }
+    if (brute) {
+        if (profile) k_smem_wavefront<true, true><<<grid, kSwBlock, smem, st>>>(sv, f, out);
+        else k_smem_wavefront<true, false><<<grid, kSwBlock, smem, st>>>(sv, f, out);
+    } else {
+        if (profile) k_smem_wavefront<false, true><<<grid, kSwBlock, smem, st>>>(sv, f, out);
+        else k_smem_wavefront<false, false><<<grid, kSwBlock, smem, st>>>(sv, f, out);
+    }
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    if (profile) PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[1], st));
+    if (stats) {
+        std::vector<uint4> bs(grid);
+        std::vector<uint32_t> it(grid);
+        PT_CUDA_CHECK(ctx, cudaMemcpyAsync(bs.data(), out.block_stats, 16 * (size_t)grid, cudaMemcpyDeviceToHost, st));
+        PT_CUDA_CHECK(ctx, cudaMemcpyAsync(it.data(), out.block_iters, 4 * (size_t)grid, cudaMemcpyDeviceToHost, st));
+        std::vector<unsigned long long> clk(profile ? 3 * (size_t)grid : 0);
+        if (profile) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(clk.data(), out.block_clk, 24 * (size_t)grid, cudaMemcpyDeviceToHost, st));
+        PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
+        uint64_t a = 0, b = 0, c = 0, d = 0, itmax = 0;
+        for (auto& v : bs) { a += v.x; b += v.y; c += v.z; d += v.w; }
+        for (auto v : it) itmax = v > itmax ? v : itmax;
+        stats->samples = f.total_work;
+        stats->rays_primary = a; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
+        stats->wavefront_iters = itmax; stats->kernel_launches = 1; stats->path_pool = grid * kSwSlots;
+        stats->n_kernel[PT_K_SMEM_WAVEFRONT] = 1;
+        if (profile) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ctx->prof_events[0], ctx->prof_events[1]);
+            stats->ms_kernel[PT_K_SMEM_WAVEFRONT] = ms;
+            double t = 0, sh = 0, h = 0;
+            for (size_t k = 0; k < grid; ++k) { t += (double)clk[3 * k]; sh += (double)clk[3 * k + 1]; h += (double)clk[3 * k + 2]; }
+            double tot = t + sh + h;
+            if (tot > 0) { stats->phase_share[0] = (float)(t / tot); stats->phase_share[1] = (float)(sh / tot); stats->phase_share[2] = (float)(h / tot); }
+        }
+    }
+    return PT_OK;
+}

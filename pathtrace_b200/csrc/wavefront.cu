@@ -16,10 +16,9 @@
 #include <cstdio>
 #include <vector>
 
-#include "pt_internal.h"
-#include "pt_shade.cuh"
+#include "pt_wave.cuh"
 
-using namespace ptd;
+using namespace ptw;
 
 namespace {
 
@@ -36,8 +35,6 @@ constexpr int kBlock = 256;
 constexpr int kShadeBlock = PT_SHADE_BLOCK, kShadeMinBlocks = PT_SHADE_MIN_BLOCKS;
 constexpr int kShadeSlots = PT_SHADE_SLOTS;   // path slots owned by one shade CTA (a multiple of kShadeBlock and of kBlock)
 constexpr int kItersPerBatch = 16;
-constexpr int kStackDepth = 64;
-constexpr uint32_t kMaxSmemPrims = 1024;   // scene staged in shared memory up to this many objects
 
 // device counter block (uint64 words)
 // device counter block (uint64 words); every counter sits in its own 256-byte line so their L2 atomics do not serialise
@@ -59,35 +56,6 @@ struct Pool {
     unsigned long long* block_next;   // per shade-CTA: next work item of its private, contiguous work range
 };
 
-struct Frame {
-    CameraDev cam;
-    uint32_t npix;
-    uint64_t total_work;     // npix * spp of this call
-    uint64_t chunk;          // work items owned by each shade-CTA (contiguous range)
-    uint32_t sample_offset, min_depth, max_depth, strategy;
-    uint32_t k0, k1;         // Philox key
-    float t_min;
-    float4* accum;           // per pixel: sum r, g, b, (reserved)
-};
-
-struct SceneView {
-    const float4* prims;
-    const float4* mats;
-    const uint32_t* light_ids;
-    const float4* nodes;
-    uint32_t n_objects, n_lights, n_nodes;
-};
-
-PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
-    uint32_t sample = f.sample_offset + (uint32_t)(w / f.npix);
-    uint32_t pixel = (uint32_t)(w % f.npix);
-    uint32_t x = pixel % f.cam.width, y = pixel / f.cam.width;
-    uint4 r = philox4x32_10(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
-    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, u01(r.x), u01(r.y));   // world.rs:299
-    ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
-    rd = make_float4(d.x, d.y, d.z, 0.0f);
-    meta = make_uint2(pixel | 0x80000000u, sample & 0x00ffffffu);
-}
 
 // K1 — initial fill of the pool.  Work is partitioned statically: shade-CTA b owns the contiguous work range
 // [b*chunk, (b+1)*chunk) and hands it out to its own kShadeBlock slots (no global work counter, no global atomics).
@@ -112,122 +80,6 @@ __global__ void __launch_bounds__(kBlock) k_generate(Pool pool, const __grid_con
     }
 }
 
-// ------------------------------------------------------------------------------------ traversal
-// Scene staged in shared memory: [nodes: 4 float4 each][prims: 3 float4 each (q0,q1,q2)]
-template <bool SMEM>
-struct Geo {
-    const float4* nodes;
-    const float4* prims;   // stride 3 (smem) or 4 (global)
-    PT_DEV void node(int i, float4& a, float4& b, float4& c, float4& d) const {
-        if (SMEM) { a = nodes[4 * i]; b = nodes[4 * i + 1]; c = nodes[4 * i + 2]; d = nodes[4 * i + 3]; }
-        else { a = __ldg(nodes + 4 * i); b = __ldg(nodes + 4 * i + 1); c = __ldg(nodes + 4 * i + 2); d = __ldg(nodes + 4 * i + 3); }
-    }
-    PT_DEV void prim(int i, float4& q0, float4& q1, float4& q2) const {
-        if (SMEM) { q0 = prims[3 * i]; q1 = prims[3 * i + 1]; q2 = prims[3 * i + 2]; }
-        else { q0 = __ldg(prims + 4 * (size_t)i); q1 = __ldg(prims + 4 * (size_t)i + 1); q2 = __ldg(prims + 4 * (size_t)i + 2); }
-    }
-};
-template <bool SMEM>
-PT_DEV Geo<SMEM> stage_scene(const SceneView& s, float4* smem, bool want_nodes) {
-    Geo<SMEM> g;
-    if (SMEM) {
-        uint32_t nn = want_nodes ? s.n_nodes * 4 : 0;
-        for (uint32_t i = threadIdx.x; i < nn; i += blockDim.x) smem[i] = __ldg(s.nodes + i);
-        for (uint32_t i = threadIdx.x; i < s.n_objects * 3; i += blockDim.x) smem[nn + i] = __ldg(s.prims + 4 * (i / 3) + (i % 3));
-        __syncthreads();
-        g.nodes = smem; g.prims = smem + nn;
-    } else {
-        g.nodes = s.nodes; g.prims = s.prims;
-    }
-    return g;
-}
-
-// Slab test against [lo,hi]; conservative: NaN slabs (0 * inf) are ignored, far side widened by 2 ulp.
-PT_DEV bool slab(float3 lo, float3 hi, float3 ro, float3 inv, float t_min, float t_max, float& tnear) {
-    float tx0 = (lo.x - ro.x) * inv.x, tx1 = (hi.x - ro.x) * inv.x;
-    float ty0 = (lo.y - ro.y) * inv.y, ty1 = (hi.y - ro.y) * inv.y;
-    float tz0 = (lo.z - ro.z) * inv.z, tz1 = (hi.z - ro.z) * inv.z;
-    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), t_min));
-    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), t_max));
-    tnear = tn;
-    return tn <= tf * 1.0000004f;
-}
-
-// Closest hit.  Winner = smallest t in [t_min, inf); equal t -> higher object index (world.rs:281-287 scans
-// in index order with an inclusive t_max, so a later object replaces an earlier one on a tie).
-template <bool SMEM, bool BRUTE>
-PT_DEV void closest_hit(const Geo<SMEM>& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
-    best_t = FLT_MAX; best_id = -1;
-    float tmax = __int_as_float(0x7f800000);
-    auto test = [&](int id) {
-        float4 q0, q1, q2;
-        g.prim(id, q0, q1, q2);
-        float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
-        if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
-    };
-    if (BRUTE) {
-        for (int id = 0; id < (int)n_objects; ++id) test(id);
-    } else {
-        float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
-        int stack[kStackDepth];
-        int sp = 0, node = 0;
-        while (true) {
-            float4 a, b, c, d;
-            g.node(node, a, b, c, d);
-            int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
-            float tl, tr;
-            bool hl = slab(v3(a), v3(b), ro, inv, t_min, tmax, tl);
-            bool hr = slab(v3(c), v3(d), ro, inv, t_min, tmax, tr);
-            if (hl && cl < 0) { test(~cl); hl = false; }
-            if (hr && cr < 0) { test(~cr); hr = false; }
-            if (hl && hr) {
-                if (tr < tl) { int t = cl; cl = cr; cr = t; }
-                stack[sp++] = cr; node = cl;
-            } else if (hl) node = cl;
-            else if (hr) node = cr;
-            else { if (sp == 0) break; node = stack[--sp]; }
-        }
-    }
-    if (best_id >= 0) best_t = tmax;
-}
-// Any hit in [t_min, t_max] (rendering.rs:62-65)
-template <bool SMEM, bool BRUTE>
-PT_DEV bool any_hit(const Geo<SMEM>& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float t_max) {
-    if (BRUTE) {
-        bool occluded = false;
-        for (int id = 0; id < (int)n_objects; ++id) {
-            float4 q0, q1, q2;
-            g.prim(id, q0, q1, q2);
-            occluded |= hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f;
-        }
-        return occluded;
-    }
-    float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
-    int stack[kStackDepth];
-    int sp = 0, node = 0;
-    while (true) {
-        float4 a, b, c, d;
-        g.node(node, a, b, c, d);
-        int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
-        float tl, tr;
-        bool hl = slab(v3(a), v3(b), ro, inv, t_min, t_max, tl);
-        bool hr = slab(v3(c), v3(d), ro, inv, t_min, t_max, tr);
-        if (hl && cl < 0) {
-            float4 q0, q1, q2; g.prim(~cl, q0, q1, q2);
-            if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
-            hl = false;
-        }
-        if (hr && cr < 0) {
-            float4 q0, q1, q2; g.prim(~cr, q0, q1, q2);
-            if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
-            hr = false;
-        }
-        if (hl && hr) { stack[sp++] = cr; node = cl; }
-        else if (hl) node = cl;
-        else if (hr) node = cr;
-        else { if (sp == 0) return false; node = stack[--sp]; }
-    }
-}
 
 // K3 — closest hit for every live slot
 template <bool SMEM, bool BRUTE>
@@ -289,24 +141,6 @@ PT_DEV Compact block_compact(bool flag, uint64_t* counter, uint32_t* s_warp, uns
     return r;
 }
 
-// rendering.rs:91-98
-PT_DEV float rr_prob(const Frame& f, float3 tn, uint32_t depth) {
-    if (depth < f.min_depth) return 1.0f;
-    float l = fminf(luminance(tn), 1.0f);
-    if (depth >= f.max_depth) l *= exp2f(-(float)(depth - f.min_depth));
-    return l;
-}
-
-// meta packing: x = pixel | alive << 31, y = sample | depth << 24
-PT_DEV uint2 pack_meta(uint32_t pixel, uint32_t sample, uint32_t depth, bool alive) {
-    return make_uint2(pixel | (alive ? 0x80000000u : 0u), (sample & 0x00ffffffu) | (depth << 24));
-}
-#define META_ALIVE(m) (((m).x >> 31) != 0u)
-#define META_PIXEL(m) ((m).x & 0x7fffffffu)
-#define META_SAMPLE(m) ((m).y & 0x00ffffffu)
-#define META_DEPTH(m) ((m).y >> 24)
-
-enum { CLS_MIRROR = 0, CLS_DIFFUSE = 1, CLS_EMISSIVE = 2, CLS_MISS = 3, CLS_DEAD = 4, CLS_COUNT = 5 };
 
 // K4 + K6 + K7 (+ K8 accumulate, + K1 regeneration).
 // Work per path varies by an order of magnitude (miss ~ nothing, diffuse vertex ~ 500 instructions, GGX vertex ~ 1400), so
@@ -335,6 +169,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool poo
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t base = blockIdx.x * kShadeSlots;
     const bool mis = f.strategy == PT_STRATEGY_MIS;
+    const SceneGlobal sg{s.prims, s.mats, s.light_ids, s.n_lights};
     const uint64_t work_lo = (uint64_t)blockIdx.x * f.chunk, work_hi = work_lo + f.chunk < f.total_work ? work_lo + f.chunk : f.total_work;
 
     // ---- phase 0
@@ -405,80 +240,22 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool poo
         float sh_tmax = 0.f;
         if (alive) {
             const uint2 h = s_hit[j];
-            const uint32_t depth = META_DEPTH(meta);
             if (h.y == 0xffffffffu) {
                 finished = true;                                  // background is black, rendering.rs:140-141
             } else {
                 const float4 ro4 = pool.ray_o[i], rd4 = pool.ray_d[i];
-                const float3 ro = v3(ro4), rd = v3(rd4);
                 const float3 beta = v3(pool.beta[i]);
-                const int obj = (int)h.y;
-                const float t = __uint_as_float(h.x);
-                float4 q0 = __ldg(s.prims + 4 * (size_t)obj), q1 = __ldg(s.prims + 4 * (size_t)obj + 1);
-                float4 q2 = __ldg(s.prims + 4 * (size_t)obj + 2), q3 = __ldg(s.prims + 4 * (size_t)obj + 3);
-                Mat m = load_mat(s.mats, obj);
-                float3 p = ro + rd * t;
-                const bool is_tri = __float_as_uint(q0.w) == PT_KIND_TRIANGLE;
-                float3 n_out = is_tri ? v3(q3) : (p - v3(q0)) / q1.x;     // shape.rs:195 / :86
-                const bool front = dot(rd, n_out) < 0.0f;                 // base.rs:20
-                float3 n = front ? n_out : -n_out;
-                if (m.kind == PT_MATK_EMISSIVE && dot(m.color, m.color) > 0.0f) {
-                    // rendering.rs:42-49 for a primary ray; :106-121 (look-ahead MIS) for a scattered ray
-                    float3 L;
-                    if (depth == 0) L = m.color;
-                    else if (!mis) L = beta * m.color;                    // rendering.rs:226-228
-                    else {
-                        float ps;                                         // shape pdf from the previous vertex, NOT / n_lights (Q2)
-                        if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), ro, p, ld, dd); }
-                        else ps = sphere_pdf_omega(v3(q0), q1.x, ro);
-                        float pb = rd4.w;
-                        L = beta * (m.color * (pb / (pb + ps)));
-                    }
-                    finished = true;
-                    add_L = true; Ladd = L;
-                } else {
-                    c_vertex++;
-                    const uint32_t pixel = META_PIXEL(meta), sample = META_SAMPLE(meta);
-                    uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
-                    uint4 b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
-                    // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by K5
-                    bool want_shadow = false;
-                    if (mis && s.n_lights > 0) {
-                        uint32_t li = __ldg(s.light_ids + urange(b0.x, s.n_lights));
-                        float4 l0 = __ldg(s.prims + 4 * (size_t)li), l1 = __ldg(s.prims + 4 * (size_t)li + 1);
-                        float4 l2 = __ldg(s.prims + 4 * (size_t)li + 2), l3 = __ldg(s.prims + 4 * (size_t)li + 3);
-                        float3 le = v3(__ldg(s.mats + 2 * (size_t)li));
-                        float3 ldir; float dist, pdf_shape;
-                        sample_light_shape(l0, l1, l2, l3, p, u01(b0.y), u01(b0.z), ldir, dist, pdf_shape);
-                        float pl = pdf_shape / (float)s.n_lights;         // world.rs:260
-                        float cos_theta = fabsf(dot(n, ldir));            // rendering.rs:68
-                        float3 fe; float pb;
-                        bsdf_eval(m, rd, ro4.w, ldir, n, fe, pb);         // inherited eta_ratio (Q3)
-                        float w_nee = pl / (pl + pb);
-                        float3 c = beta * fe * le * (w_nee * cos_theta / pl);
-                        if (finite3(c) && (c.x != 0.f || c.y != 0.f || c.z != 0.f)) {
-                            want_shadow = true;
-                            sh_o = p; sh_d = ldir; sh_c = c; sh_tmax = dist - 0.001f;   // rendering.rs:64
-                        }
-                    }
-                    // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
-                    float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
-                    float3 wo, fs; float pdf, cos_s;
-                    bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.w), u01(b1.x), u01(b1.y), wo, fs, pdf, cos_s);
-                    float3 tn = beta * fs * (cos_s / pdf);
-                    ok = ok && finite3(tn);
-                    float q = ok ? rr_prob(f, tn, depth) : 0.0f;
-                    if (!ok || u01(b1.z) > q) {
-                        finished = true;                                  // D of this vertex is dropped too (Q1)
-                    } else {
-                        emit_shadow = want_shadow;
-                        float3 nb = tn / q;
-                        pool.beta[i] = make_float4(nb.x, nb.y, nb.z, 0.f);
-                        pool.ray_o[i] = make_float4(p.x, p.y, p.z, eta_new);      // rendering.rs:86-87
-                        pool.ray_d[i] = make_float4(wo.x, wo.y, wo.z, pdf);
-                        pool.meta[i] = pack_meta(pixel, sample, depth + 1, true);
-                        c_scatter++;
-                    }
+                VertexOut vo = shade_vertex(sg, f, mis, ro4, rd4, beta, h, meta);
+                finished = vo.finished; add_L = vo.add_L; Ladd = vo.Ladd;
+                c_vertex += vo.vertex ? 1u : 0u;
+                if (!vo.finished) {
+                    emit_shadow = vo.emit_shadow;
+                    sh_o = v3(vo.new_ro); sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
+                    pool.beta[i] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
+                    pool.ray_o[i] = vo.new_ro;
+                    pool.ray_d[i] = vo.new_rd;
+                    pool.meta[i] = vo.new_meta;
+                    c_scatter++;
                 }
             }
         }
@@ -576,27 +353,6 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary(SceneView s, const __g
     if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
 }
 
-SceneView make_view(const SceneDev& d) {
-    SceneView v;
-    v.prims = d.prims; v.mats = d.mats; v.light_ids = d.light_ids; v.nodes = d.nodes;
-    v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
-    return v;
-}
-Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {
-    Frame f;
-    f.cam.origin = make_float3(c.origin[0], c.origin[1], c.origin[2]);
-    f.cam.llc = make_float3(c.lower_left_corner[0], c.lower_left_corner[1], c.lower_left_corner[2]);
-    f.cam.horizontal = make_float3(c.horizontal[0], c.horizontal[1], c.horizontal[2]);
-    f.cam.vertical = make_float3(c.vertical[0], c.vertical[1], c.vertical[2]);
-    f.cam.width = c.width; f.cam.height = c.height;
-    f.npix = c.width * c.height;
-    f.total_work = (uint64_t)f.npix * p.spp;
-    f.sample_offset = p.sample_offset; f.min_depth = p.min_depth; f.max_depth = p.max_depth; f.strategy = p.strategy;
-    f.k0 = (uint32_t)p.seed; f.k1 = (uint32_t)(p.seed >> 32);
-    f.t_min = p.t_min;
-    f.accum = accum;
-    return f;
-}
 struct Mode { bool smem, brute; size_t smem_bytes; };
 Mode pick_mode(const SceneDev& s, uint32_t traversal) {
     Mode m;
@@ -662,7 +418,7 @@ int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t 
 
 int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
                             float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches) {
-    SceneView sv = make_view(scene);
+    SceneView sv = make_scene_view(scene);
     Frame f = make_frame(cam, prm, nullptr);
     Mode mode = pick_mode(scene, prm.traversal);
     uint32_t grid = (f.npix + kBlock - 1) / kBlock;
@@ -706,11 +462,14 @@ static int ensure_pool(pt_context* ctx, uint32_t P, Pool& pool) {
 int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     cudaStream_t st = ctx->stream;
     const SceneDev& scene = *rl.scene;
-    SceneView sv = make_view(scene);
+    SceneView sv = make_scene_view(scene);
     Frame f = make_frame(rl.cam, rl.prm, rl.d_accum);
     Mode mode = pick_mode(scene, rl.prm.traversal);
     uint64_t launches = 0, iters = 0;
     if (f.total_work == 0) { if (stats) { stats->samples = 0; } return PT_OK; }
+    // small scenes: queues in shared memory, one persistent launch (smem_wavefront.cu)
+    if (!(rl.prm.flags & PT_FLAG_HBM_QUEUES) && smem_wavefront_applicable(ctx, scene, mode.brute))
+        return smem_wavefront_render(ctx, rl, mode.brute, stats);
 
     // default pool: 4 full waves of shade CTAs (SMs x resident CTAs x slots per CTA), i.e. 2.4 M paths on a 148-SM B200
     uint32_t P = rl.prm.path_pool ? rl.prm.path_pool : (uint32_t)ctx->sm_count * kShadeMinBlocks * kShadeSlots * 4u;
@@ -730,8 +489,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     const uint32_t sgrid = P / kShadeSlots;
     f.chunk = (f.total_work + sgrid - 1) / sgrid;
     const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
-    float ms_k[PT_K_COUNT] = {0, 0, 0, 0};
-    uint32_t n_k[PT_K_COUNT] = {0, 0, 0, 0};
+    float ms_k[PT_K_COUNT] = {0, 0, 0, 0, 0};
+    uint32_t n_k[PT_K_COUNT] = {0, 0, 0, 0, 0};
     std::vector<int> ev_class;
     size_t ev_used = 0;
     auto prof_begin = [&](int cls) {
