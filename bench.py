@@ -154,7 +154,7 @@ def run_ours(args, rank, world, local_rank):
     h_radiance = torch.empty(npix, 3, dtype=torch.float32).pin_memory()
     h_rgba = torch.empty(npix, 4, dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, device=dev, dtype=torch.uint8)   # > 126 MB L2
-    params = api.render_params(spp=spp_g, sample_offset=off_g, path_pool=args.pool, profile=args.profile_in_timed)
+    params = api.render_params(spp=spp_g, sample_offset=off_g, path_pool=args.pool, profile=args.profile_in_timed, hbm_queues=args.hbm_queues)
     totals = {"launches": 0, "rays": 0, "samples": 0, "stats": []}
 
     def barrier():
@@ -239,7 +239,7 @@ def run_ours(args, rank, world, local_rank):
         if args.profile_in_timed:
             prof_stats = dev_stats
         else:   # same workload, PT_FLAG_PROFILE on: events around every launch (outside the timed region)
-            pp = api.render_params(spp=spp_g, sample_offset=off_g, path_pool=args.pool, profile=True)
+            pp = api.render_params(spp=spp_g, sample_offset=off_g, path_pool=args.pool, profile=True, hbm_queues=args.hbm_queues)
             with torch.cuda.stream(ext):
                 accum.zero_()
                 prof_stats = [api.render_accumulate_device(ctx, scene, cam, pp, accum.data_ptr())]
@@ -256,6 +256,7 @@ def run_ours(args, rank, world, local_rank):
             verts = sum(s["path_vertices"] for s in prof_stats)
             flops = {"trace_closest": fl["flops_closest_per_ray"] * r_closest, "trace_shadow": fl["flops_shadow_per_ray"] * r_shadow,
                      "shade": fl["flops_shade_per_vertex"] * verts, "generate": 0.0}
+            flops["smem_wavefront"] = flops["trace_closest"] + flops["trace_shadow"] + flops["shade"]   # all stages in one launch
             dom = max(kernel_ms, key=kernel_ms.get)
             ach = flops[dom] / (kernel_ms[dom] * 1e-3) / 1e12
             whole = fl["flops_per_sample"] * value * 1e6 / 1e12
@@ -263,16 +264,27 @@ def run_ours(args, rank, world, local_rank):
                         "traffic": None, "peak_source": "in-run FFMA microbenchmark (pt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
                         "peak_nominal": fp32_nominal, "frac_of_nominal": ach / fp32_nominal,
                         "launches": n_kernel[dom], "avg_launch_ms": kernel_ms[dom] / max(n_kernel[dom], 1),
-                        "algorithmic_flops_per_ray": fl["flops_closest_per_ray"] if dom == "trace_closest" else fl["flops_shadow_per_ray"] if dom == "trace_shadow" else fl["flops_shade_per_vertex"],
+                        "algorithmic_flops_per_unit": {"closest_ray": fl["flops_closest_per_ray"], "shadow_ray": fl["flops_shadow_per_ray"],
+                                                       "shade_vertex": fl["flops_shade_per_vertex"], "sample": fl["flops_per_sample"]},
+                        "units_per_launch": {"closest_rays": r_closest / max(n_kernel[dom], 1), "shadow_rays": r_shadow / max(n_kernel[dom], 1),
+                                             "vertices": verts / max(n_kernel[dom], 1)},
+                        "phase_share": prof_stats[0].get("phase_share"),
                         "kernel_share_of_step": kernel_ms[dom] / max(sum(kernel_ms.values()), 1e-9),
                         "whole_step": {"flops_per_sample": fl["flops_per_sample"], "achieved": whole, "frac": whole / fp32_tf},
                         "note": "algorithmic flops counted from the reference's arithmetic by the oracle's counting scalar (FMA=2, no re-trace)"}
             # queue traffic (implementation overhead, reported separately; never added to roofline.achieved)
-            qb = 56.0 * r_closest + 200.0 * verts + 64.0 * r_shadow
             t_all = sum(kernel_ms.values()) * 1e-3
-            roofline_hbm = {"bound": "hbm", "what": "wavefront queue traffic (path state, hits, shadow queue)", "achieved": qb / t_all / 1e9,
-                            "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": qb / t_all / 1e9 / peaks["hbm_gbs"], "peak_source": peaks_src,
-                            "bytes_per_ray_closest": 56, "bytes_per_vertex_shade": 200, "bytes_per_shadow_ray": 64}
+            if dom == "smem_wavefront":
+                # queues live in shared memory: HBM sees only the float4 accumulate atomics (16 B each, L2-resident frame)
+                qb = 16.0 * (r_shadow + sum(s["samples"] for s in prof_stats))
+                roofline_hbm = {"bound": "hbm", "what": "upper bound on accumulate traffic: one 16-byte float4 atomic per finished path and per shadow ray; "
+                                "ray / hit / path-state / shadow queues are in shared memory and never reach HBM", "achieved": qb / t_all / 1e9,
+                                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": qb / t_all / 1e9 / peaks["hbm_gbs"], "peak_source": peaks_src}
+            else:
+                qb = 56.0 * r_closest + 200.0 * verts + 64.0 * r_shadow
+                roofline_hbm = {"bound": "hbm", "what": "wavefront queue traffic (path state, hits, shadow queue)", "achieved": qb / t_all / 1e9,
+                                "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": qb / t_all / 1e9 / peaks["hbm_gbs"], "peak_source": peaks_src,
+                                "bytes_per_ray_closest": 56, "bytes_per_vertex_shade": 200, "bytes_per_shadow_ray": 64}
             # ---- CPU baseline: the oracle (port of the reference's CPU path) on this box's host cores, bounded sample
             if world == 1 and not args.no_cpu_baseline:
                 oc = oracle_cam(O, cam)
@@ -292,7 +304,8 @@ def run_ours(args, rank, world, local_rank):
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "width": WIDTH, "height": HEIGHT, "spp": spp_total, "spp_per_gpu": spp_g, "strategy": "mis",
                        "parallelism": f"spp-split x{world} + 1 NCCL reduce(sum)", "path_pool": st0["path_pool"],
-                       "l2": "explicit 256 MiB write between steps; path-state working set also exceeds L2"},
+                       "formulation": "hbm-queue wavefront" if args.hbm_queues else "shared-memory wavefront (one persistent launch)",
+                       "l2": "explicit 256 MiB write between steps"},
             "mrays_per_s": rays / (ms_total * 1e-3) / 1e6, "rays_per_sample": rays / max(samples, 1),
             "gpu_launches": int(launches), "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -318,6 +331,7 @@ def main():
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU-baseline sample")
     ap.add_argument("--ref-spp", type=int, default=2, help="spp per step of the --impl reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--hbm-queues", action="store_true", help="force the HBM-queue wavefront (one launch per stage per bounce)")
     ap.add_argument("--profile-in-timed", action="store_true", help="record per-kernel events inside the timed steps")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

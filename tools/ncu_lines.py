@@ -1,6 +1,6 @@
 """Per-source-line instruction and stall-sample totals of one kernel from an ncu report (development helper).
 
-  python tools/ncu_lines.py REPORT.ncu-rep KERNEL_REGEX [launch_skip] [top_n]
+  python tools/ncu_lines.py REPORT.ncu-rep KERNEL_REGEX[::MANGLED_REGEX] [launch_skip] [top_n]
 
 ncu's CSV source page is SASS-only, so the SASS rows (in program order) are joined with the line table that
 `nvdisasm -g` prints for the cubin embedded in the in-tree library (compiled with -lineinfo).
@@ -48,9 +48,12 @@ def line_table(kernel_re):
 
 def main():
     rep, kre = sys.argv[1], sys.argv[2]
+    nre = kre                      # "ncu_regex::mangled_regex" when the demangled and mangled names need different patterns
+    if "::" in kre:
+        nre, kre = kre.split("::", 1)
     skip = sys.argv[3] if len(sys.argv) > 3 else "0"
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-    txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{kre}", "--launch-skip", skip,
+    txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{nre}", "--launch-skip", skip,
                           "--launch-count", "1"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(txt)))
     hdr_i = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
