@@ -146,8 +146,8 @@ def run_ours(args, rank, world, local_rank):
     scene = api.Scene(ctx, sh, mt)
     npix = WIDTH * HEIGHT
     spp_total = args.spp
-    spp_g = spp_total // world + (1 if rank < spp_total % world else 0)
-    off_g = rank * (spp_total // world) + min(rank, spp_total % world)
+    from pathtrace_b200.distributed import split_spp
+    spp_g, off_g = split_spp(spp_total, world, rank)
     accum = torch.zeros(npix, 4, device=dev, dtype=torch.float32)
     radiance = torch.empty(npix, 3, device=dev, dtype=torch.float32)
     rgba = torch.empty(npix, 4, device=dev, dtype=torch.uint8)
