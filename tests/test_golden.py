@@ -82,23 +82,31 @@ def test_converged_image_matches_reference(hbm_queues, gpu_ctx):
     sc.close()
     a = a.astype(np.float64); b = b.astype(np.float64)
     gpu = 0.5 * (a + b)
-    gpu_var = 0.25 * (a - b) ** 2                  # unbiased estimate of Var[(a+b)/2] per pixel (1 dof: use it in aggregate only)
-    diff = gpu - ref
-    mse = (diff ** 2).mean(axis=(0, 1))
-    noise = (gpu_var + ref_var).mean(axis=(0, 1))
-    debiased = mse - noise
-    print("spp", spp_g, "mse", mse, "noise", noise, "debiased", debiased, "rmse", np.sqrt(np.maximum(debiased, 0)))
-    assert np.all(debiased <= (1e-3) ** 2 + 0.05 * noise), (debiased, noise)
-    # z-scores with a smoothed GPU variance (the reference's per-pixel variance scaled by the spp ratio)
-    z = diff / np.sqrt(ref_var * (1.0 + int(g["spp"]) / spp_g) + 1e-12)
-    ok = ref_var > 0
-    frac3 = (np.abs(z[ok]) > 3).mean()
-    print("fraction |z|>3:", frac3, "mean z:", z[ok].mean(), "std z:", z[ok].std())
-    assert frac3 < 0.02                            # normal tail is 0.27 %; fireflies of the glass caustics widen it
-    assert abs(z[ok].mean()) < 0.1
-    # no spatial structure: mean z over 16x16 tiles stays within +-4 standard errors of a tile mean
-    tiles = z[..., 1].reshape(10, 16, 10, 16).mean(axis=(1, 3))
-    assert np.abs(tiles).max() < 4.0 / 16.0 * 1.5, np.abs(tiles).max()
+    gpu_var = 0.25 * (a - b) ** 2                  # unbiased estimate of Var[(a+b)/2] per pixel (1 dof: used in aggregates only)
+    diff, tot = gpu - ref, gpu_var + ref_var
+    # (1) RMSE with the Monte Carlo noise of both sides removed.  The ~180 pixels straddling the edge of the light carry a
+    # binomial variance 1000x the rest (15 or ~0.3 per sample) and would dominate the estimator's own error, so they are
+    # judged by their z-scores instead.
+    lum_var = ref_var.sum(axis=2)
+    body = lum_var < 30 * np.median(lum_var)
+    assert 50 < (~body).sum() < 400
+    debiased = (diff ** 2 - tot)[body].mean(axis=0)
+    se = np.sqrt(2.0 * (tot[body] ** 2).sum(axis=0)) / body.sum()       # standard error of `debiased` itself
+    print("spp", spp_g, "debiased MSE", debiased, "its SE", se, "RMSE", np.sqrt(np.maximum(debiased, 0)))
+    assert np.all(debiased <= (1e-3) ** 2 + 3.0 * se), (debiased, se)
+    z_edge = diff[~body] / np.sqrt(tot[~body] + 1e-30)
+    assert np.sqrt((z_edge ** 2).mean()) < 1.6 and np.abs(z_edge).max() < 6.0
+    # (2) z-scores aggregated over 16x16 tiles: Z = sum(diff) / sqrt(sum(var)).  (A per-pixel studentised z is biased for
+    # this right-skewed estimator because a pixel's variance estimate is correlated with its mean; sums over a tile are not.)
+    num = diff.reshape(10, 16, 10, 16, 3).sum(axis=(1, 3))
+    den = np.sqrt(tot.reshape(10, 16, 10, 16, 3).sum(axis=(1, 3)))
+    Z = num / den
+    print("tile Z: rms", np.sqrt((Z ** 2).mean()), "mean", Z.mean(), "max", np.abs(Z).max())
+    assert 0.7 < np.sqrt((Z ** 2).mean()) < 1.35          # ~N(0,1): no excess error, no spatial structure
+    assert np.abs(Z).max() < 4.5 and abs(Z.mean()) < 0.6
+    frac3 = (np.abs(Z) > 3).mean()
+    assert frac3 < 0.02                                     # normal tail: 0.27 %
+    # (3) energy: global mean within 0.2 %
     assert abs(gpu.mean() - ref.mean()) / ref.mean() < 2e-3
 
 
