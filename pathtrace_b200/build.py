@@ -17,6 +17,11 @@ SOURCES = ["capi.cu", "lbvh.cu", "wavefront.cu", "smem_wavefront.cu"]
 HEADERS = ["pt_internal.h", "pt_math.cuh", "pt_shade.cuh", "pt_wave.cuh", os.path.join("..", "..", "include", "pathtrace_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "-ccbin", "g++"]
+# The render kernels compile plain `/` and sqrtf() to the approximate MUFU sequences (2 ulp): that is the free-form shading
+# math (statistical parity only).  Everything under the bit-exact contract (camera rays, intersection, LBVH) is written with
+# explicit __f*_rn intrinsics, which these flags do not touch; denormals and FMA contraction keep their defaults.
+FAST_SHADING_FLAGS = ["-prec-div=false", "-prec-sqrt=false"]
+FAST_SHADING_SOURCES = {"wavefront.cu", "smem_wavefront.cu"}
 
 
 def _nvcc() -> str:
@@ -44,7 +49,8 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("PT_NVCC_EXTRA", "").split(), "-c", os.path.join(CSRC, src), "-o", obj]
+        fast = FAST_SHADING_FLAGS if src in FAST_SHADING_SOURCES and not os.environ.get("PT_PRECISE_SHADING") else []
+        cmd = [nvcc, *NVCC_FLAGS, *fast, *os.environ.get("PT_NVCC_EXTRA", "").split(), "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

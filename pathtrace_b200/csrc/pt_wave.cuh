@@ -99,7 +99,7 @@ PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, fl
     if (BRUTE) {
         for (int id = 0; id < (int)n_objects; ++id) test(id);
     } else {
-        float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
+        float3 inv = v3(__frcp_rn(rd.x), __frcp_rn(rd.y), __frcp_rn(rd.z));   // exact: the slab margins assume IEEE reciprocals
         int stack[kStackDepth];
         int sp = 0, node = 0;
         while (true) {
@@ -133,7 +133,7 @@ PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float 
         }
         return occluded;
     }
-    float3 inv = v3(1.0f / rd.x, 1.0f / rd.y, 1.0f / rd.z);
+    float3 inv = v3(__frcp_rn(rd.x), __frcp_rn(rd.y), __frcp_rn(rd.z));   // exact: the slab margins assume IEEE reciprocals
     int stack[kStackDepth];
     int sp = 0, node = 0;
     while (true) {
