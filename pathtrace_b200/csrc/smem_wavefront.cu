@@ -23,14 +23,21 @@ using namespace ptw;
 
 namespace {
 
+// One CTA of 1024 threads per SM owning 3072 slots: the class sort sees a window wide enough that almost every 32-slot
+// tile is a single class (measured: 512-slot windows lose ~12 % to mixed tiles), and 3 rays per thread keep phase T balanced.
 #ifndef PT_SW_BLOCK
-#define PT_SW_BLOCK 256
+#define PT_SW_BLOCK 1024
 #endif
 #ifndef PT_SW_SPT
-#define PT_SW_SPT 2
+#define PT_SW_SPT 3
 #endif
 #ifndef PT_SW_MIN_BLOCKS
-#define PT_SW_MIN_BLOCKS 4
+#define PT_SW_MIN_BLOCKS 1
+#endif
+// 1: a vertex traces its own shadow ray right after it is shaded (no shadow queue: 32 B per slot less shared memory, one
+// barrier less, no partially filled last round).  0: shadow rays go through a compacted shared-memory queue and a phase H.
+#ifndef PT_SW_INLINE_SHADOW
+#define PT_SW_INLINE_SHADOW 1
 #endif
 constexpr int kSwBlock = PT_SW_BLOCK, kSwSpt = PT_SW_SPT, kSwSlots = kSwBlock * kSwSpt, kSwMinBlocks = PT_SW_MIN_BLOCKS;
 
@@ -43,7 +50,7 @@ struct SwOut {
 // Bytes of dynamic shared memory for a scene (must match the carve-up in the kernel).
 size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bool brute) {
     size_t b = 0;
-    b += 16 * (size_t)kSwSlots * 5;                 // ro, rd, beta, shadow d, shadow c
+    b += 16 * (size_t)kSwSlots * (PT_SW_INLINE_SHADOW ? 3 : 5);   // ro, rd, beta (, shadow d, shadow c)
     b += 8 * (size_t)kSwSlots * 2;                  // hit, meta
     b += 16 * ((brute ? 0 : (size_t)n_nodes * 4) + (size_t)n_objects * 4 + (size_t)n_objects * 2);
     b += 4 * (((size_t)n_lights + 3) & ~size_t(3));
@@ -58,9 +65,13 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     float4* s_ro = smem;
     float4* s_rd = s_ro + kSwSlots;
     float4* s_beta = s_rd + kSwSlots;
+#if PT_SW_INLINE_SHADOW
+    uint2* s_hit = reinterpret_cast<uint2*>(s_beta + kSwSlots);
+#else
     float4* s_shd = s_beta + kSwSlots;                 // shadow queue: direction.xyz, t_max
     float4* s_shc = s_shd + kSwSlots;                  // contribution.rgb, slot bits
     uint2* s_hit = reinterpret_cast<uint2*>(s_shc + kSwSlots);
+#endif
     uint2* s_meta = s_hit + kSwSlots;
     float4* s_nodes = reinterpret_cast<float4*>(s_meta + kSwSlots);
     float4* s_prims = s_nodes + (BRUTE ? 0 : s.n_nodes * 4);
@@ -68,6 +79,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     uint32_t* s_lights = reinterpret_cast<uint32_t*>(s_mats + s.n_objects * 2);
     uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));
     __shared__ uint16_t s_cls_cnt[CLS_COUNT][SPT * NW];
+    __shared__ uint32_t s_cls_total[CLS_COUNT];
     __shared__ unsigned long long s_next;      // this CTA's next work item
     __shared__ uint32_t s_shadow, s_tile, s_alive;
     __shared__ unsigned long long s_clk[4];    // PROF: t_prev, T+S, A, H
@@ -133,22 +145,34 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         }
         if (tid == 0) { s_shadow = 0; s_tile = 0; s_alive = 0; }
         __syncthreads();
-        // ---- phase S: exclusive prefix over the CLS_COUNT x (SPT*NW) counts in (class, group) order, one warp
-        if (tid < 32) {
-            constexpr uint32_t N = CLS_COUNT * SPT * NW;
-            uint16_t* flat = &s_cls_cnt[0][0];
+        // ---- phase S: counting sort by class.  Warp cc scans the SPT*NW group counts of class cc (exclusive, in place);
+        // the class bases are the running sum of the five totals.
+        for (uint32_t cc = warp; cc < CLS_COUNT; cc += NW) {
+            constexpr uint32_t N = SPT * NW;
+            uint16_t* row = s_cls_cnt[cc];
             uint32_t run = 0;
             for (uint32_t k0 = 0; k0 < N; k0 += 32) {
-                uint32_t k = k0 + tid;
-                uint32_t v = k < N ? flat[k] : 0, x = v;
+                uint32_t k = k0 + lane;
+                uint32_t v = k < N ? row[k] : 0, x = v;
                 for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-                if (k < N) flat[k] = (uint16_t)(run + x - v);
+                if (k < N) row[k] = (uint16_t)(run + x - v);
                 run += __shfl_sync(0xffffffffu, x, 31);
             }
+            if (lane == 0) s_cls_total[cc] = run;
         }
         __syncthreads();
+        {
+            uint32_t start[CLS_COUNT], acc = 0;
 #pragma unroll
-        for (int k = 0; k < SPT; ++k) s_order[s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)(k * kSwBlock + tid);
+            for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) { start[cc] = acc; acc += s_cls_total[cc]; }
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) {
+                uint32_t st = 0;
+#pragma unroll
+                for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) st = cls[k] == cc ? start[cc] : st;
+                s_order[st + s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)(k * kSwBlock + tid);
+            }
+        }
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[1] += t - s_clk[0]; s_clk[0] = t; }
 
@@ -165,8 +189,10 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             bool finished = false, emit_shadow = false, add_L = false, vertex = false;
             float3 Ladd = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
             float sh_tmax = 0.f;
+            float3 p_hit = v3(0.f, 0.f, 0.f);
             if (alive) {
                 VertexOut vo = shade_vertex(sc, f, mis, s_ro[j], s_rd[j], v3(s_beta[j]), s_hit[j], meta);
+                p_hit = v3(vo.new_ro);
                 finished = vo.finished; add_L = vo.add_L; Ladd = vo.Ladd; vertex = vo.vertex;
                 if (!vo.finished) {
                     emit_shadow = vo.emit_shadow; sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
@@ -174,6 +200,13 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                     s_beta[j] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
                 }
             }
+#if PT_SW_INLINE_SHADOW
+            // K5 inline: the shadow ray starts at the hit point (the new ray origin) and is traced by the lane that shaded
+            // the vertex; unoccluded contributions go straight to the pixel (rendering.rs:62-80).
+            if (emit_shadow && !any_hit<true, BRUTE>(g, s.n_objects, p_hit, sh_d, f.t_min, sh_tmax))
+                atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
+            c_shadow += __popc(__ballot_sync(0xffffffffu, emit_shadow));
+#else
             // shadow queue compaction: warp ballot/popc + one shared-memory atomic per warp.  The ray starts at the new
             // origin of slot j (the hit point), so an entry is (direction, t_max, contribution, slot).
             {
@@ -187,9 +220,10 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                     s_shc[e] = make_float4(sh_c.x, sh_c.y, sh_c.z, __uint_as_float(j));
                 }
                 c_shadow += __popc(bal);
-                c_vertex += __popc(__ballot_sync(0xffffffffu, vertex));
-                c_scatter += __popc(__ballot_sync(0xffffffffu, alive && !finished));
             }
+#endif
+            c_vertex += __popc(__ballot_sync(0xffffffffu, vertex));
+            c_scatter += __popc(__ballot_sync(0xffffffffu, alive && !finished));
             // K8 accumulate (world.rs:296-313) + regeneration from this CTA's private work range
             {
                 uint32_t bal = __ballot_sync(0xffffffffu, finished);
@@ -214,8 +248,12 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         }
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
-        const uint32_t alive_now = s_alive, n_sh = s_shadow;
+        const uint32_t alive_now = s_alive;
+#if !PT_SW_INLINE_SHADOW
+        const uint32_t n_sh = s_shadow;
+#endif
 
+#if !PT_SW_INLINE_SHADOW
         // ---- phase H: any-hit over the compacted shadow queue (dense: every warp is full except the last)
         for (uint32_t e = tid; e < n_sh; e += kSwBlock) {
             float4 d = s_shd[e], c = s_shc[e];
@@ -224,6 +262,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             if (!any_hit<true, BRUTE>(g, s.n_objects, v3(o), v3(d), f.t_min, d.w))
                 atomicAdd(f.accum + META_PIXEL(s_meta[j]), make_float4(c.x, c.y, c.z, 0.f));   // rendering.rs:70-80
         }
+#endif
         ++iters;
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[3] += t - s_clk[0]; s_clk[0] = t; }
@@ -252,7 +291,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
 bool smem_wavefront_applicable(const pt_context* ctx, const SceneDev& scene, bool brute) {
     (void)ctx;
     size_t bytes = sw_smem_bytes(scene.n_objects, scene.n_nodes, scene.n_lights, brute) + 1024;
-    return scene.n_objects > 0 && scene.n_objects <= kMaxSmemPrims && bytes * 3 <= 227 * 1024;
+    return scene.n_objects > 0 && scene.n_objects <= kMaxSmemPrims && bytes * (kSwMinBlocks < 3 ? kSwMinBlocks : 3) <= 227 * 1024;
 }
 
 int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, pt_stats* stats) {
