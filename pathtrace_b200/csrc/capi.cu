@@ -127,6 +127,11 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
             if (std::sqrt((double)e[0] * e[0] + (double)e[1] * e[1] + (double)e[2] * e[2]) > 0.0) lights.push_back(i);
         }
     sc->dev.n_lights = (uint32_t)lights.size();
+    if (n && n <= 1024) {   // brute-force scan table: consecutive triangles share an entry (lbvh.cu: k_brute_table walks the same way)
+        uint32_t e = 0;
+        for (uint32_t i = 0; i < n; ++e) i += (i + 1 < n && shapes[i].kind == PT_SHAPE_TRIANGLE && shapes[i + 1].kind == PT_SHAPE_TRIANGLE) ? 2 : 1;
+        sc->dev.n_brute = e;
+    }
     pt_shape* d_shapes = nullptr;
     pt_material* d_mats = nullptr;
     auto cleanup = [&](int rc) { if (d_shapes) cudaFree(d_shapes); if (d_mats) cudaFree(d_mats); if (rc) { pt_scene_destroy(sc); } return keep(ctx, rc); };
@@ -154,7 +159,7 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
 void pt_scene_destroy(pt_scene* sc) {
     if (!sc) return;
     if (sc->ctx) cudaSetDevice(sc->ctx->device);
-    void* ptrs[] = {sc->dev.prims, sc->dev.mats, sc->dev.light_ids, sc->dev.nodes, sc->dev.codes_sorted, sc->dev.prim_sorted};
+    void* ptrs[] = {sc->dev.prims, sc->dev.mats, sc->dev.light_ids, sc->dev.nodes, sc->dev.codes_sorted, sc->dev.prim_sorted, sc->dev.brute};
     for (void* p : ptrs) if (p) cudaFree(p);
     delete sc;
 }

@@ -15,6 +15,8 @@ struct SceneDev {
     float4* mats = nullptr;       // 2 x float4 per object (32 B): see pt_shade.cuh
     uint32_t* light_ids = nullptr;
     float4* nodes = nullptr;      // 4 x float4 per LBVH node (64 B): [Llo,left][Lhi,right][Rlo,0][Rhi,0]
+    float4* brute = nullptr;      // brute-force scan table, 5 x float4 per entry (see k_brute_table); scenes <= 1024 objects only
+    uint32_t n_brute = 0;
     uint32_t* codes_sorted = nullptr;
     uint32_t* prim_sorted = nullptr;
     float bounds[6] = {0, 0, 0, 0, 0, 0};

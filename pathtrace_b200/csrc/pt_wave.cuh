@@ -30,6 +30,8 @@ struct SceneView {
     const uint32_t* light_ids;
     const float4* nodes;
     uint32_t n_objects, n_lights, n_nodes;
+    const float4* brute;     // brute-force scan table (may be null)
+    uint32_t n_brute;
 };
 
 PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
@@ -48,6 +50,8 @@ PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uin
 template <bool SMEM, int PS = 3>
 struct Geo {
     const float4* nodes;
+    const float4* brute = nullptr;   // smem copy of the brute-force scan table, n_brute entries of 5 float4 (null: scan prims)
+    uint32_t n_brute = 0;
     const float4* prims;   // stride PS (smem: 3 = q0,q1,q2 only; 4 = with the normal) or 4 (global)
     PT_DEV void node(int i, float4& a, float4& b, float4& c, float4& d) const {
         if (SMEM) { a = nodes[4 * i]; b = nodes[4 * i + 1]; c = nodes[4 * i + 2]; d = nodes[4 * i + 3]; }
@@ -62,6 +66,12 @@ template <bool SMEM>
 PT_DEV Geo<SMEM> stage_scene(const SceneView& s, float4* smem, bool want_nodes) {
     Geo<SMEM> g;
     if (SMEM) {
+        if (!want_nodes && s.brute) {        // brute force: only the scan table is needed
+            for (uint32_t i = threadIdx.x; i < s.n_brute * 5; i += blockDim.x) smem[i] = __ldg(s.brute + i);
+            __syncthreads();
+            g.nodes = smem; g.prims = smem; g.brute = smem; g.n_brute = s.n_brute;
+            return g;
+        }
         uint32_t nn = want_nodes ? s.n_nodes * 4 : 0;
         for (uint32_t i = threadIdx.x; i < nn; i += blockDim.x) smem[i] = __ldg(s.nodes + i);
         for (uint32_t i = threadIdx.x; i < s.n_objects * 3; i += blockDim.x) smem[nn + i] = __ldg(s.prims + 4 * (i / 3) + (i % 3));
@@ -96,7 +106,25 @@ PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, fl
         float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
         if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
     };
-    if (BRUTE) {
+    if (BRUTE && SMEM && g.brute) {
+        // Scan table in ascending object order; consecutive triangles come as packed pairs (pt_math.cuh: hit_triangle2).  Both
+        // tests of a pair see the t_max in force before the pair and the updates re-check the inclusive bound in index order:
+        // the same winner as the sequential scan of world.rs:281-287 (ties go to the later object).
+        for (uint32_t e = 0; e < g.n_brute; ++e) {
+            const float4 A = g.brute[5 * e], B = g.brute[5 * e + 1], C = g.brute[5 * e + 2], E = g.brute[5 * e + 4];
+            const int ida = __float_as_int(E.z), idb = __float_as_int(E.w);
+            if (idb >= 0) {
+                const float4 D = g.brute[5 * e + 3];
+                float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
+                                         pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax);
+                if (t.x >= 0.0f && t.x <= tmax) { tmax = t.x; best_id = ida; }
+                if (t.y >= 0.0f && t.y <= tmax) { tmax = t.y; best_id = idb; }
+            } else {
+                float t = hit_prim(A, B, C, ro, rd, t_min, tmax);
+                if (t >= 0.0f && t <= tmax) { tmax = t; best_id = ida; }
+            }
+        }
+    } else if (BRUTE) {
         for (int id = 0; id < (int)n_objects; ++id) test(id);
     } else {
         float3 inv = v3(__frcp_rn(rd.x), __frcp_rn(rd.y), __frcp_rn(rd.z));   // exact: the slab margins assume IEEE reciprocals
@@ -124,6 +152,21 @@ PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, fl
 // Any hit in [t_min, t_max] (rendering.rs:62-65)
 template <bool SMEM, bool BRUTE, class G>
 PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float t_max) {
+    if (BRUTE && SMEM && g.brute) {
+        bool occluded = false;
+        for (uint32_t e = 0; e < g.n_brute; ++e) {
+            const float4 A = g.brute[5 * e], B = g.brute[5 * e + 1], C = g.brute[5 * e + 2], E = g.brute[5 * e + 4];
+            if (__float_as_int(E.w) >= 0) {
+                const float4 D = g.brute[5 * e + 3];
+                float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
+                                         pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, t_max);
+                occluded |= (t.x >= 0.0f) | (t.y >= 0.0f);
+            } else {
+                occluded |= hit_prim(A, B, C, ro, rd, t_min, t_max) >= 0.0f;
+            }
+        }
+        return occluded;
+    }
     if (BRUTE) {
         bool occluded = false;
         for (int id = 0; id < (int)n_objects; ++id) {
@@ -298,6 +341,7 @@ inline SceneView make_scene_view(const SceneDev& d) {
     SceneView v;
     v.prims = d.prims; v.mats = d.mats; v.light_ids = d.light_ids; v.nodes = d.nodes;
     v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
+    v.brute = d.brute; v.n_brute = d.n_brute;
     return v;
 }
 inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {

@@ -54,7 +54,8 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
     b += 8 * (size_t)kSwSlots * 2;                  // hit, meta
     b += 16 * ((brute ? 0 : (size_t)n_nodes * 4) + (size_t)n_objects * 4 + (size_t)n_objects * 2);
     b += 4 * (((size_t)n_lights + 3) & ~size_t(3));
-    b += 2 * (size_t)kSwSlots;                      // sorted order
+    b += 2 * (((size_t)kSwSlots + 7) & ~size_t(7));  // sorted order
+    b += brute ? 16 * 5 * (size_t)n_objects : 0;    // brute-force scan table (at most one entry per object)
     return b;
 }
 
@@ -78,6 +79,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     float4* s_mats = s_prims + s.n_objects * 4;
     uint32_t* s_lights = reinterpret_cast<uint32_t*>(s_mats + s.n_objects * 2);
     uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));
+    float4* s_brute = reinterpret_cast<float4*>(s_order + ((kSwSlots + 7) & ~7));
     __shared__ uint16_t s_cls_cnt[CLS_COUNT][SPT * NW];
     __shared__ uint32_t s_cls_total[CLS_COUNT];
     __shared__ unsigned long long s_next;      // this CTA's next work item
@@ -94,6 +96,10 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     for (uint32_t i = tid; i < s.n_objects * 2; i += kSwBlock) s_mats[i] = __ldg(s.mats + i);
     for (uint32_t i = tid; i < s.n_lights; i += kSwBlock) s_lights[i] = __ldg(s.light_ids + i);
     Geo<true, 4> g; g.nodes = s_nodes; g.prims = s_prims;
+    if (BRUTE && s.brute) {
+        for (uint32_t i = tid; i < s.n_brute * 5; i += kSwBlock) s_brute[i] = __ldg(s.brute + i);
+        g.brute = s_brute; g.n_brute = s.n_brute;
+    }
     const SceneShared sc{s_prims, s_mats, s_lights, s.n_lights};
 
     // ---- K1: initial fill of this CTA's slots from its work range

@@ -358,7 +358,8 @@ Mode pick_mode(const SceneDev& s, uint32_t traversal) {
     Mode m;
     m.brute = traversal == PT_TRAVERSAL_BRUTE || (traversal == PT_TRAVERSAL_AUTO && s.n_objects <= 16);
     m.smem = s.n_objects <= kMaxSmemPrims;
-    m.smem_bytes = m.smem ? sizeof(float4) * ((m.brute ? 0 : (size_t)s.n_nodes * 4) + (size_t)s.n_objects * 3) : 0;
+    m.smem_bytes = !m.smem ? 0 : (m.brute && s.brute) ? sizeof(float4) * 5 * (size_t)s.n_brute
+                                                     : sizeof(float4) * ((m.brute ? 0 : (size_t)s.n_nodes * 4) + (size_t)s.n_objects * 3);
     return m;
 }
 template <class K> int set_smem(pt_context* ctx, K kernel, size_t bytes) {
