@@ -107,14 +107,14 @@ def run_reference(args, rank):
     sh, mt, cam = default_scene_arrays()
     oc = oracle_cam(O, cam)
     spp_step = args.ref_spp
-    threads = O.lib().pto_num_threads()
+    threads = os.cpu_count() or 1          # torchrun exports OMP_NUM_THREADS=1: ask for every host core explicitly
     samples = WIDTH * HEIGHT * spp_step
     for w in range(args.warmup):
-        O.render(oc, sh, mt, O.RenderParams(spp=1, sample_offset=w), "f64", recursive=True)
+        O.render(oc, sh, mt, O.RenderParams(spp=1, sample_offset=w), "f64", recursive=True, nthreads=threads)
     t0 = time.perf_counter()
     rays = 0
     for k in range(args.steps):
-        r = O.render(oc, sh, mt, O.RenderParams(spp=spp_step, sample_offset=1000 + k * spp_step), "f64", recursive=True)
+        r = O.render(oc, sh, mt, O.RenderParams(spp=spp_step, sample_offset=1000 + k * spp_step), "f64", recursive=True, nthreads=threads)
         c = r["counters"]
         rays += c["primary"] + c["shadow"] + c["scattered"]
     dt = time.perf_counter() - t0
@@ -132,6 +132,7 @@ def run_reference(args, rank):
 
 # ------------------------------------------------------------------------------------------------ our arm
 def run_ours(args, rank, world, local_rank):
+    import gc
     import torch
     import torch.distributed as dist
     from pathtrace_b200 import api
@@ -139,11 +140,30 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    dev = torch.device("cuda", local_rank)
     ctx = api.Context(local_rank)
-    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     sh, mt, cam = default_scene_arrays()
     scene = api.Scene(ctx, sh, mt)
+    try:
+        _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam)
+    finally:
+        # every tensor that touched the library's stream must be gone before that stream is destroyed
+        gc.collect()
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        scene.close()
+        ctx.close()
+
+
+def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
+    import torch
+    import torch.distributed as dist
+    from pathtrace_b200 import api
+
+    dev = torch.device("cuda", local_rank)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
     npix = WIDTH * HEIGHT
     spp_total = args.spp
     from pathtrace_b200.distributed import split_spp
@@ -288,9 +308,10 @@ def run_ours(args, rank, world, local_rank):
             # ---- CPU baseline: the oracle (port of the reference's CPU path) on this box's host cores, bounded sample
             if world == 1 and not args.no_cpu_baseline:
                 oc = oracle_cam(O, cam)
-                O.render(oc, sh, mt, O.RenderParams(spp=1), "f64", recursive=True)
-                r = O.render(oc, sh, mt, O.RenderParams(spp=args.cpu_spp, sample_offset=7), "f64", recursive=True)
-                cpu_baseline = {"value": npix * args.cpu_spp / r["seconds"] / 1e6, "unit": "Msamples/s", "cores": O.lib().pto_num_threads(),
+                ncpu = os.cpu_count() or 1
+                O.render(oc, sh, mt, O.RenderParams(spp=1), "f64", recursive=True, nthreads=ncpu)
+                r = O.render(oc, sh, mt, O.RenderParams(spp=args.cpu_spp, sample_offset=7), "f64", recursive=True, nthreads=ncpu)
+                cpu_baseline = {"value": npix * args.cpu_spp / r["seconds"] / 1e6, "unit": "Msamples/s", "cores": ncpu,
                                 "kind": "port", "sample": f"{WIDTH}x{HEIGHT} at {args.cpu_spp} spp (of {SPP}); f64, brute-force scan, recursive MIS with re-trace, OpenMP dynamic per pixel",
                                 "seconds": r["seconds"]}
         except Exception as e:   # the oracle is a checker; the bench line survives without it
@@ -313,11 +334,7 @@ def run_ours(args, rank, world, local_rank):
                             "scene upload per rank + render + NCCL reduce + resolve + D2H on rank 0"},
             "roofline": roofline, "roofline_hbm": roofline_hbm, "kernel_ms": kernel_ms, "cpu_baseline": cpu_baseline,
         }
-        print(json.dumps(line))
-    scene.close()
-    ctx.close()
-    if world > 1:
-        dist.destroy_process_group()
+        print(json.dumps(line), flush=True)
 
 
 def main():
