@@ -21,6 +21,7 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
 
 import numpy as np  # noqa: E402
 
@@ -79,6 +80,17 @@ def measured_peaks():
         with open(p) as f:
             return json.load(f), "MEASURED_PEAKS.json"
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` on this workload, from the committed
+    `ncu --set full` capture (profiles/roofline_traffic.json; null when no capture of this kernel exists)."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        with open(p) as f:
+            return json.load(f).get(kernel, {}).get("bytes_per_launch")
+    except (OSError, ValueError):
+        return None
 
 
 def default_scene_arrays():
@@ -281,7 +293,7 @@ def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
             ach = flops[dom] / (kernel_ms[dom] * 1e-3) / 1e12
             whole = fl["flops_per_sample"] * value * 1e6 / 1e12
             roofline = {"bound": "fp32", "kernel": "k_" + dom, "achieved": ach, "peak": fp32_tf, "unit": "TFLOP/s", "frac": ach / fp32_tf,
-                        "traffic": None, "peak_source": "in-run FFMA microbenchmark (pt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
+                        "traffic": ncu_traffic("k_" + dom), "peak_source": "in-run FFMA microbenchmark (pt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 entry",
                         "peak_nominal": fp32_nominal, "frac_of_nominal": ach / fp32_nominal,
                         "launches": n_kernel[dom], "avg_launch_ms": kernel_ms[dom] / max(n_kernel[dom], 1),
                         "algorithmic_flops_per_unit": {"closest_ray": fl["flops_closest_per_ray"], "shadow_ray": fl["flops_shadow_per_ray"],
