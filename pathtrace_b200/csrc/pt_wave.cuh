@@ -115,10 +115,11 @@ PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, fl
             const int ida = __float_as_int(E.z), idb = __float_as_int(E.w);
             if (idb >= 0) {
                 const float4 D = g.brute[5 * e + 3];
+                bool oka, okb;
                 float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
-                                         pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax);
-                if (t.x >= 0.0f && t.x <= tmax) { tmax = t.x; best_id = ida; }
-                if (t.y >= 0.0f && t.y <= tmax) { tmax = t.y; best_id = idb; }
+                                         pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax, oka, okb);
+                if (oka) { tmax = t.x; best_id = ida; }
+                if (okb & (t.y <= tmax)) { tmax = t.y; best_id = idb; }
             } else {
                 float t = hit_prim(A, B, C, ro, rd, t_min, tmax);
                 if (t >= 0.0f && t <= tmax) { tmax = t; best_id = ida; }
@@ -158,9 +159,10 @@ PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float 
             const float4 A = g.brute[5 * e], B = g.brute[5 * e + 1], C = g.brute[5 * e + 2], E = g.brute[5 * e + 4];
             if (__float_as_int(E.w) >= 0) {
                 const float4 D = g.brute[5 * e + 3];
-                float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
-                                         pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, t_max);
-                occluded |= (t.x >= 0.0f) | (t.y >= 0.0f);
+                bool oka, okb;
+                hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
+                              pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, t_max, oka, okb);
+                occluded |= oka | okb;
             } else {
                 occluded |= hit_prim(A, B, C, ro, rd, t_min, t_max) >= 0.0f;
             }

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         s_next = work_lo + kSwSlots;
         if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = s_clk[3] = 0; }
     }
-    uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // meaningful on lane 0 of each warp / tid 0
+    uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // per-lane counters, reduced once at the end
     __syncthreads();
 
     while (true) {
@@ -183,6 +183,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[1] += t - s_clk[0]; s_clk[0] = t; }
 
         // ---- phase A: dynamic tiles of the class-sorted slot list
+        uint32_t n_alive = 0;
         while (true) {
             uint32_t tile = 0;
             if (lane == 0) tile = atomicAdd(&s_tile, 1u);
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             // the vertex; unoccluded contributions go straight to the pixel (rendering.rs:62-80).
             if (emit_shadow && !any_hit<true, BRUTE>(g, s.n_objects, p_hit, sh_d, f.t_min, sh_tmax))
                 atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
-            c_shadow += __popc(__ballot_sync(0xffffffffu, emit_shadow));
+            c_shadow += emit_shadow ? 1u : 0u;
 #else
             // shadow queue compaction: warp ballot/popc + one shared-memory atomic per warp.  The ray starts at the new
             // origin of slot j (the hit point), so an entry is (direction, t_max, contribution, slot).
@@ -225,11 +226,11 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                     s_shd[e] = make_float4(sh_d.x, sh_d.y, sh_d.z, sh_tmax);
                     s_shc[e] = make_float4(sh_c.x, sh_c.y, sh_c.z, __uint_as_float(j));
                 }
-                c_shadow += __popc(bal);
+                c_shadow += emit_shadow ? 1u : 0u;
             }
 #endif
-            c_vertex += __popc(__ballot_sync(0xffffffffu, vertex));
-            c_scatter += __popc(__ballot_sync(0xffffffffu, alive && !finished));
+            c_vertex += vertex ? 1u : 0u;
+            c_scatter += (alive && !finished) ? 1u : 0u;
             // K8 accumulate (world.rs:296-313) + regeneration from this CTA's private work range
             {
                 uint32_t bal = __ballot_sync(0xffffffffu, finished);
@@ -248,10 +249,11 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                         alive = false;
                     }
                 }
-                uint32_t na = __popc(__ballot_sync(0xffffffffu, alive));
-                if (lane == 0 && na) atomicAdd(&s_alive, na);
+                n_alive += alive ? 1u : 0u;
             }
         }
+        n_alive = __reduce_add_sync(0xffffffffu, n_alive);
+        if (lane == 0 && n_alive) atomicAdd(&s_alive, n_alive);
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
         const uint32_t alive_now = s_alive;
@@ -279,6 +281,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     __shared__ uint32_t s_stats[3];
     if (tid < 3) s_stats[tid] = 0;
     __syncthreads();
+    c_shadow = __reduce_add_sync(0xffffffffu, c_shadow); c_scatter = __reduce_add_sync(0xffffffffu, c_scatter); c_vertex = __reduce_add_sync(0xffffffffu, c_vertex);
     if (lane == 0) { atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex); }
     __syncthreads();
     if (tid == 0) {
