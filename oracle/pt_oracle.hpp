@@ -153,6 +153,10 @@ inline U4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint
 template <class T> inline T u01(uint32_t x) { return T(((double)(x >> 9) + 0.5) * (1.0 / 8388608.0)); }
 // rng.random_range(0..n) (world.rs:255): widening multiply
 inline uint32_t urange(uint32_t x, uint32_t n) { return (uint32_t)(((uint64_t)x * n) >> 32); }
+// Random word for the light pick: the low byte of each word of block 0 (u01 uses bits 9..31 of the same words, so the
+// light index is independent of the four uniforms).  Block 0 = [light r1, light r2, bsdf r1, bsdf r2]; block 1 =
+// [lobe u, roulette u, -, -] and is only needed by GGX surfaces and from the roulette depth on (the device skips it otherwise).
+inline uint32_t light_word(const U4& b) { return (b.w[0] & 0xffu) | ((b.w[1] & 0xffu) << 8) | ((b.w[2] & 0xffu) << 16) | ((b.w[3] & 0xffu) << 24); }
 
 struct RngKey {
     uint32_t k0, k1, pixel, sample;
@@ -694,7 +698,7 @@ template <class T> struct World {
         U4 b0 = rng.block(depth, 0), b1 = rng.block(depth, 1);
         Vec3<T> total = Vec3<T>::zero(), direct = Vec3<T>::zero();
         LightSample<T> ls;
-        if (sample_light_point(hit, b0.w[0], u01<T>(b0.w[1]), u01<T>(b0.w[2]), ls)) {   // :56
+        if (sample_light_point(hit, light_word(b0), u01<T>(b0.w[0]), u01<T>(b0.w[1]), ls)) {   // :56
             Vec3<T> to_light = ls.point - hit.point;
             T distance = to_light.length();
             Vec3<T> light_dir = to_light.normalize();
@@ -711,13 +715,13 @@ template <class T> struct World {
         }
         total += direct / T(1);   // NUM_LIGHT_SAMPLES = 1, :81
         ray.eta_ratio = get_eta_from_object(obj, hit);   // :83
-        BsdfSample<T> bs = materials[obj].bsdf_pdf_sample(ray, hit.normal, u01<T>(b0.w[3]), u01<T>(b1.w[0]), u01<T>(b1.w[1]));
+        BsdfSample<T> bs = materials[obj].bsdf_pdf_sample(ray, hit.normal, u01<T>(b0.w[2]), u01<T>(b0.w[3]), u01<T>(b1.w[0]));
         Ray<T> scattered(hit.point, bs.dir);
         scattered.eta_ratio = get_eta_from_object(obj, hit);   // :87
         Vec3<T> next_tp = throughput * bs.f * bs.cos_theta / bs.pdf;   // :89
         if (!(bs.pdf > T(0)) || !m_finite(next_tp.x) || !m_finite(next_tp.y) || !m_finite(next_tp.z)) return Vec3<T>::zero();
         T q = rr_prob(next_tp, depth);
-        if (u01<T>(b1.w[2]) > q) return Vec3<T>::zero();   // :100-102 (drops `direct` too, Q1)
+        if (u01<T>(b1.w[1]) > q) return Vec3<T>::zero();   // :100-102 (drops `direct` too, Q1)
         HitRecord<T> h2; uint32_t o2 = 0;
         if (rc) rc->scattered++;
         if (hit_scene(scattered, t_min, inf(), h2, o2)) {   // :104-105
@@ -742,13 +746,13 @@ template <class T> struct World {
         if (to_double(emitted.length()) > 0.0) return emitted;
         U4 b0 = rng.block(depth, 0), b1 = rng.block(depth, 1);
         ray.eta_ratio = get_eta_from_object(obj, hit);
-        BsdfSample<T> bs = materials[obj].bsdf_pdf_sample(ray, hit.normal, u01<T>(b0.w[3]), u01<T>(b1.w[0]), u01<T>(b1.w[1]));
+        BsdfSample<T> bs = materials[obj].bsdf_pdf_sample(ray, hit.normal, u01<T>(b0.w[2]), u01<T>(b0.w[3]), u01<T>(b1.w[0]));
         Ray<T> scattered(hit.point, bs.dir);
         scattered.eta_ratio = get_eta_from_object(obj, hit);
         Vec3<T> next_tp = throughput * bs.f * bs.cos_theta / bs.pdf;
         if (!(bs.pdf > T(0)) || !m_finite(next_tp.x) || !m_finite(next_tp.y) || !m_finite(next_tp.z)) return Vec3<T>::zero();
         T q = rr_prob(next_tp, depth);
-        if (u01<T>(b1.w[2]) > q) return Vec3<T>::zero();
+        if (u01<T>(b1.w[1]) > q) return Vec3<T>::zero();
         Vec3<T> incoming = ray_color_brdf_only(scattered, depth + 1, rng, next_tp / q, rc);
         return bs.f * incoming * bs.cos_theta / (bs.pdf * q);
     }
@@ -772,7 +776,7 @@ template <class T> struct World {
             U4 b0 = rng.block(depth, 0), b1 = rng.block(depth, 1);
             Vec3<T> D = Vec3<T>::zero();
             LightSample<T> ls;
-            if (mis && sample_light_point(hit, b0.w[0], u01<T>(b0.w[1]), u01<T>(b0.w[2]), ls)) {
+            if (mis && sample_light_point(hit, light_word(b0), u01<T>(b0.w[0]), u01<T>(b0.w[1]), ls)) {
                 Vec3<T> to_light = ls.point - hit.point;
                 T distance = to_light.length();
                 Vec3<T> light_dir = to_light.normalize();
@@ -789,11 +793,11 @@ template <class T> struct World {
                 }
             }
             ray.eta_ratio = get_eta_from_object(obj, hit);
-            BsdfSample<T> bs = materials[obj].bsdf_pdf_sample(ray, hit.normal, u01<T>(b0.w[3]), u01<T>(b1.w[0]), u01<T>(b1.w[1]));
+            BsdfSample<T> bs = materials[obj].bsdf_pdf_sample(ray, hit.normal, u01<T>(b0.w[2]), u01<T>(b0.w[3]), u01<T>(b1.w[0]));
             Vec3<T> tn = beta * bs.f * bs.cos_theta / bs.pdf;
             if (!(bs.pdf > T(0)) || !m_finite(tn.x) || !m_finite(tn.y) || !m_finite(tn.z)) return L;
             T q = rr_prob(tn, depth);
-            if (u01<T>(b1.w[2]) > q) return L;
+            if (u01<T>(b1.w[1]) > q) return L;
             L += beta * D;
             beta = tn / q;
             Ray<T> scattered(hit.point, bs.dir);

@@ -243,11 +243,13 @@ __global__ void k_pack_scene(const pt_shape* __restrict__ shapes, const pt_mater
     float3 a = make_float3(s.v[0], s.v[1], s.v[2]);
     if (s.kind == PT_SHAPE_TRIANGLE) {
         float3 e1 = ptd::xsub(make_float3(s.v[3], s.v[4], s.v[5]), a), e2 = ptd::xsub(make_float3(s.v[6], s.v[7], s.v[8]), a);
-        float3 nn = ptd::xnormalize(ptd::xcross(e1, e2));   // shape.rs:195
+        float3 cr = ptd::xcross(e1, e2);
+        float3 nn = ptd::xnormalize(cr);   // shape.rs:195
+        float area = __fmul_rn(__fsqrt_rn(ptd::xdot(cr, cr)), 0.5f);   // shape.rs:228, used by the light pdf only
         prims[4 * i + 0] = make_float4(a.x, a.y, a.z, __uint_as_float(PT_KIND_TRIANGLE));
         prims[4 * i + 1] = make_float4(e1.x, e1.y, e1.z, 0.f);
         prims[4 * i + 2] = make_float4(e2.x, e2.y, e2.z, 0.f);
-        prims[4 * i + 3] = make_float4(nn.x, nn.y, nn.z, 0.f);
+        prims[4 * i + 3] = make_float4(nn.x, nn.y, nn.z, area);
     } else {
         prims[4 * i + 0] = make_float4(a.x, a.y, a.z, __uint_as_float(PT_KIND_SPHERE));
         prims[4 * i + 1] = make_float4(s.v[3], 0.f, 0.f, 0.f);

@@ -203,8 +203,8 @@ PT_DEV bool bsdf_sample(const Mat& m, float3 rd, float eta, float3 n, float r1, 
 
 // ------------------------------------------------------------------------------------ light sampling, shape.rs
 // TriangleShape::sample_surface_from_point pdf part, :215-240: solid-angle pdf of point p seen from x.
-PT_DEV float triangle_pdf_omega(float3 e1, float3 e2, float3 nrm, float3 x, float3 p, float3& ldir, float& d) {
-    float area = length(cross(e1, e2)) * 0.5f;
+// `area` = |e1 x e2| / 2, stored with the primitive (q3.w) when the scene is packed.
+PT_DEV float triangle_pdf_omega(float area, float3 nrm, float3 x, float3 p, float3& ldir, float& d) {
     float3 tl = p - x;
     d = length(tl);
     ldir = tl / d;
@@ -229,7 +229,7 @@ PT_DEV void sample_light_shape(float4 q0, float4 q1, float4 q2, float4 q3, float
         float sq = sqrtf(r1);
         float u = 1.0f - sq, v = r2 * sq;
         float3 p = v3(q0) + v3(q1) * u + v3(q2) * v;
-        pdf_omega = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), x, p, ldir, d);
+        pdf_omega = triangle_pdf_omega(q3.w, v3(q3), x, p, ldir, d);
     } else {
         float3 c = v3(q0);
         float radius = q1.x;

@@ -287,7 +287,7 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
         else if (!mis) L = beta * m.color;                    // rendering.rs:226-228
         else {
             float ps;                                         // shape pdf from the previous vertex, NOT / n_lights (Q2)
-            if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(v3(q1), v3(q2), v3(q3), ro, p, ld, dd); }
+            if (is_tri) { float3 ld; float dd; ps = triangle_pdf_omega(q3.w, v3(q3), ro, p, ld, dd); }
             else ps = sphere_pdf_omega(v3(q0), q1.x, ro);
             float pb = rd4.w;
             L = beta * (m.color * (pb / (pb + ps)));
@@ -297,17 +297,22 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
     }
     o.vertex = true;
     const uint32_t pixel = META_PIXEL(meta), sample = META_SAMPLE(meta);
+    // block 0 = [light r1, light r2, bsdf r1, bsdf r2] (+ the light pick from the low byte of each word); block 1 =
+    // [lobe u, roulette u]: only GGX surfaces choose a lobe and roulette starts at min_depth (q == 1 before), so most vertices
+    // never generate it.
     uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
-    uint4 b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
+    uint4 b1 = make_uint4(0u, 0u, 0u, 0u);
+    if (m.kind == PT_MATK_MIRROR || depth >= f.min_depth) b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
     // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by the shadow stage
     bool want_shadow = false;
     if (mis && sc.n_lights > 0) {
-        uint32_t li = sc.light(urange(b0.x, sc.n_lights));
+        uint32_t lw = (b0.x & 0xffu) | ((b0.y & 0xffu) << 8) | ((b0.z & 0xffu) << 16) | ((b0.w & 0xffu) << 24);
+        uint32_t li = sc.light(urange(lw, sc.n_lights));
         float4 l0, l1, l2, l3;
         sc.prim((int)li, l0, l1, l2, l3);
         float3 le = sc.emission((int)li);
         float3 ldir; float dist, pdf_shape;
-        sample_light_shape(l0, l1, l2, l3, p, u01(b0.y), u01(b0.z), ldir, dist, pdf_shape);
+        sample_light_shape(l0, l1, l2, l3, p, u01(b0.x), u01(b0.y), ldir, dist, pdf_shape);
         float pl = pdf_shape / (float)sc.n_lights;        // world.rs:260
         float cos_theta = fabsf(dot(n, ldir));            // rendering.rs:68
         float3 fe; float pb;
@@ -322,11 +327,11 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
     // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
     float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
     float3 wo, fs; float pdf, cos_s;
-    bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.w), u01(b1.x), u01(b1.y), wo, fs, pdf, cos_s);
+    bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.z), u01(b0.w), u01(b1.x), wo, fs, pdf, cos_s);
     float3 tn = beta * fs * (cos_s / pdf);
     ok = ok && finite3(tn);
     float q = ok ? rr_prob(f, tn, depth) : 0.0f;
-    if (!ok || u01(b1.z) > q) {
+    if (!ok || u01(b1.y) > q) {
         o.finished = true;                                  // D of this vertex is dropped too (Q1)
         return o;
     }

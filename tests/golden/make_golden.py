@@ -30,6 +30,9 @@ REF_W, REF_H, REF_SPP, REF_SEED = 160, 160, 8192, 0x601D
 
 def main():
     O.build()
+    only = sys.argv[1] if len(sys.argv) > 1 else None      # e.g. "samples": regenerate just that fixture
+    if only not in (None, "samples"):
+        raise SystemExit("usage: make_golden.py [samples]")
     # 1. primary hits
     sh, mt, cam = scenes.default_scene(96, 64)
     oc = oracle_camera(O, cam)
@@ -49,6 +52,8 @@ def main():
     rec = np.array([O.sample(oc, sh, mt, prm, int(x), int(y), int(s), "f64", True) for x, y, s in zip(xs, ys, ss)])
     itr = np.array([O.sample(oc, sh, mt, prm, int(x), int(y), int(s), "f64", False) for x, y, s in zip(xs, ys, ss)])
     np.savez_compressed(os.path.join(HERE, "samples_default_f64.npz"), x=xs, y=ys, s=ss, recursive=rec, iterative=itr)
+    if only == "samples":
+        return
     # 4. converged image
     sh, mt, cam = scenes.default_scene(REF_W, REF_H)
     oc = oracle_camera(O, cam)
