@@ -128,9 +128,12 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
         }
     sc->dev.n_lights = (uint32_t)lights.size();
     if (n && n <= 1024) {   // brute-force scan table: consecutive triangles share an entry (lbvh.cu: k_brute_table walks the same way)
-        uint32_t e = 0;
-        for (uint32_t i = 0; i < n; ++e) i += (i + 1 < n && shapes[i].kind == PT_SHAPE_TRIANGLE && shapes[i + 1].kind == PT_SHAPE_TRIANGLE) ? 2 : 1;
-        sc->dev.n_brute = e;
+        uint32_t e = 0, pairs = 0;
+        for (uint32_t i = 0; i < n; ++e) {
+            bool pair = i + 1 < n && shapes[i].kind == PT_SHAPE_TRIANGLE && shapes[i + 1].kind == PT_SHAPE_TRIANGLE;
+            pairs += pair; i += pair ? 2 : 1;
+        }
+        sc->dev.n_brute = e; sc->dev.n_pairs = pairs;
     }
     pt_shape* d_shapes = nullptr;
     pt_material* d_mats = nullptr;

@@ -278,30 +278,31 @@ __global__ void k_pack_scene(const pt_shape* __restrict__ shapes, const pt_mater
 
 }  // namespace
 
-// Brute-force scan table (small scenes): objects in index order, two consecutive triangles packed into one entry so the
-// trace kernels can test them with packed FP32 instructions.  5 float4 per entry:
+// Brute-force scan table (small scenes).  Two consecutive triangles share an entry so the trace kernels can test them with
+// packed FP32 instructions; the pair entries come first (ascending object order), the unpaired primitives after them.
+// 5 float4 per entry:
 //   pair   : (v0x_a,v0x_b,v0y_a,v0y_b) (v0z_a,v0z_b,e1x_a,e1x_b) (e1y_a,e1y_b,e1z_a,e1z_b) (e2x_a,e2x_b,e2y_a,e2y_b) (e2z_a,e2z_b,id_a,id_b)
 //   single : q0 q1 q2 of the primitive record, -, (-,-,id,-1)
-// One thread: at most 1024 objects, once per scene.  The host computes the same entry count from the shape kinds.
-__global__ void k_brute_table(const float4* __restrict__ prims, uint32_t n, float4* __restrict__ table) {
+// One thread: at most 1024 objects, once per scene.  The host computes the same entry counts from the shape kinds.
+__global__ void k_brute_table(const float4* __restrict__ prims, uint32_t n, uint32_t n_pairs, float4* __restrict__ table) {
     if (blockIdx.x || threadIdx.x) return;
-    uint32_t e = 0;
-    for (uint32_t i = 0; i < n; ++e) {
+    uint32_t ep = 0, es = n_pairs;
+    for (uint32_t i = 0; i < n;) {
         float4 a0 = prims[4 * i], a1 = prims[4 * i + 1], a2 = prims[4 * i + 2];
         bool pair = i + 1 < n && __float_as_uint(a0.w) == PT_KIND_TRIANGLE && __float_as_uint(prims[4 * (i + 1)].w) == PT_KIND_TRIANGLE;
         if (pair) {
             float4 b0 = prims[4 * (i + 1)], b1 = prims[4 * (i + 1) + 1], b2 = prims[4 * (i + 1) + 2];
-            table[5 * e + 0] = make_float4(a0.x, b0.x, a0.y, b0.y);
-            table[5 * e + 1] = make_float4(a0.z, b0.z, a1.x, b1.x);
-            table[5 * e + 2] = make_float4(a1.y, b1.y, a1.z, b1.z);
-            table[5 * e + 3] = make_float4(a2.x, b2.x, a2.y, b2.y);
-            table[5 * e + 4] = make_float4(a2.z, b2.z, __int_as_float((int)i), __int_as_float((int)i + 1));
-            i += 2;
+            table[5 * ep + 0] = make_float4(a0.x, b0.x, a0.y, b0.y);
+            table[5 * ep + 1] = make_float4(a0.z, b0.z, a1.x, b1.x);
+            table[5 * ep + 2] = make_float4(a1.y, b1.y, a1.z, b1.z);
+            table[5 * ep + 3] = make_float4(a2.x, b2.x, a2.y, b2.y);
+            table[5 * ep + 4] = make_float4(a2.z, b2.z, __int_as_float((int)i), __int_as_float((int)i + 1));
+            i += 2; ++ep;
         } else {
-            table[5 * e + 0] = a0; table[5 * e + 1] = a1; table[5 * e + 2] = a2;
-            table[5 * e + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
-            table[5 * e + 4] = make_float4(0.f, 0.f, __int_as_float((int)i), __int_as_float(-1));
-            i += 1;
+            table[5 * es + 0] = a0; table[5 * es + 1] = a1; table[5 * es + 2] = a2;
+            table[5 * es + 3] = make_float4(0.f, 0.f, 0.f, 0.f);
+            table[5 * es + 4] = make_float4(0.f, 0.f, __int_as_float((int)i), __int_as_float(-1));
+            i += 1; ++es;
         }
     }
 }
@@ -314,8 +315,14 @@ int scene_pack_launch(pt_context* ctx, const pt_shape* d_shapes, const pt_materi
         PT_CUDA_CHECK(ctx, cudaGetLastError());
         if (out.n_brute) {      // set by pt_scene_create for scenes small enough to be scanned from shared memory
             PT_CUDA_CHECK(ctx, cudaMalloc(&out.brute, sizeof(float4) * 5 * (size_t)out.n_brute));
-            k_brute_table<<<1, 32, 0, ctx->stream>>>(out.prims, n, out.brute);
+            k_brute_table<<<1, 32, 0, ctx->stream>>>(out.prims, n, out.n_pairs, out.brute);
             PT_CUDA_CHECK(ctx, cudaGetLastError());
+            const uint32_t np = out.n_pairs < (uint32_t)kBruteParamPairs ? out.n_pairs : (uint32_t)kBruteParamPairs;
+            out.brute_host.assign(5 * (size_t)np, make_float4(0.f, 0.f, 0.f, 0.f));
+            if (np) {
+                PT_CUDA_CHECK(ctx, cudaMemcpyAsync(out.brute_host.data(), out.brute, sizeof(float4) * 5 * np, cudaMemcpyDeviceToHost, ctx->stream));
+                PT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+            }
         }
     }
     return PT_OK;

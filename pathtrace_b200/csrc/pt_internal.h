@@ -8,6 +8,8 @@
 
 #include "../../include/pathtrace_b200.h"
 
+constexpr int kBruteParamPairs = 8;   // pair entries of the scan table that can travel as a kernel parameter (pt_wave.cuh: BruteParam)
+
 // Scene resident in HBM (replicated per GPU).  All arrays are float4-packed for 128-bit loads.
 struct SceneDev {
     uint32_t n_objects = 0, n_lights = 0, n_nodes = 0;
@@ -16,7 +18,8 @@ struct SceneDev {
     uint32_t* light_ids = nullptr;
     float4* nodes = nullptr;      // 4 x float4 per LBVH node (64 B): [Llo,left][Lhi,right][Rlo,0][Rhi,0]
     float4* brute = nullptr;      // brute-force scan table, 5 x float4 per entry (see k_brute_table); scenes <= 1024 objects only
-    uint32_t n_brute = 0;
+    uint32_t n_brute = 0, n_pairs = 0;   // entries; the first n_pairs are triangle pairs
+    std::vector<float4> brute_host;      // host copy of the pair entries that fit a kernel parameter (pt_wave.cuh: BruteParam)
     uint32_t* codes_sorted = nullptr;
     uint32_t* prim_sorted = nullptr;
     float bounds[6] = {0, 0, 0, 0, 0, 0};

@@ -31,7 +31,7 @@ struct SceneView {
     const float4* nodes;
     uint32_t n_objects, n_lights, n_nodes;
     const float4* brute;     // brute-force scan table (may be null)
-    uint32_t n_brute;
+    uint32_t n_brute, n_pairs;
 };
 
 PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
@@ -50,8 +50,8 @@ PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uin
 template <bool SMEM, int PS = 3>
 struct Geo {
     const float4* nodes;
-    const float4* brute = nullptr;   // smem copy of the brute-force scan table, n_brute entries of 5 float4 (null: scan prims)
-    uint32_t n_brute = 0;
+    const float4* brute = nullptr;   // smem copy of the brute-force scan table, n_brute entries of 5 float4 (null: scan prims):
+    uint32_t n_brute = 0, n_pairs = 0;   // n_pairs triangle pairs first, then the unpaired primitives
     const float4* prims;   // stride PS (smem: 3 = q0,q1,q2 only; 4 = with the normal) or 4 (global)
     PT_DEV void node(int i, float4& a, float4& b, float4& c, float4& d) const {
         if (SMEM) { a = nodes[4 * i]; b = nodes[4 * i + 1]; c = nodes[4 * i + 2]; d = nodes[4 * i + 3]; }
@@ -69,7 +69,7 @@ PT_DEV Geo<SMEM> stage_scene(const SceneView& s, float4* smem, bool want_nodes) 
         if (!want_nodes && s.brute) {        // brute force: only the scan table is needed
             for (uint32_t i = threadIdx.x; i < s.n_brute * 5; i += blockDim.x) smem[i] = __ldg(s.brute + i);
             __syncthreads();
-            g.nodes = smem; g.prims = smem; g.brute = smem; g.n_brute = s.n_brute;
+            g.nodes = smem; g.prims = smem; g.brute = smem; g.n_brute = s.n_brute; g.n_pairs = s.n_pairs;
             return g;
         }
         uint32_t nn = want_nodes ? s.n_nodes * 4 : 0;
@@ -94,6 +94,58 @@ PT_DEV bool slab(float3 lo, float3 hi, float3 ro, float3 inv, float t_min, float
     return tn <= tf * 1.0000004f;
 }
 
+// ---- brute-force scan table (lbvh.cu: k_brute_table): triangle pairs in ascending object order, then the unpaired primitives.
+// Both tests of a pair see the t_max in force before the pair and the updates re-check the inclusive bound in index order, so
+// the pairs alone reproduce the sequential scan of world.rs:281-287 (ties go to the later object).  The unpaired primitives
+// come after every pair, out of index order, and therefore break ties on the object index explicitly.
+PT_DEV void pair_closest(float4 A, float4 B, float4 C, float4 D, float4 E, float3 ro, float3 rd, float t_min, float& tmax, int& best_id) {
+    bool oka, okb;
+    float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
+                             pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax, oka, okb);
+    if (oka) { tmax = t.x; best_id = __float_as_int(E.z); }
+    if (okb & (t.y <= tmax)) { tmax = t.y; best_id = __float_as_int(E.w); }
+}
+PT_DEV void single_closest(float4 q0, float4 q1, float4 q2, float4 E, float3 ro, float3 rd, float t_min, float& tmax, int& best_id) {
+    const int id = __float_as_int(E.z);
+    float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
+    if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
+}
+PT_DEV bool pair_any(float4 A, float4 B, float4 C, float4 D, float4 E, float3 ro, float3 rd, float t_min, float t_max) {
+    bool oka, okb;
+    hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y), pk(D.z, D.w),
+                  pk(E.x, E.y), ro, rd, t_min, t_max, oka, okb);
+    return oka | okb;
+}
+// The first kParamPairs pairs of the table can also travel as a kernel parameter: the unrolled scan then takes its triangle
+// operands straight from the constant bank (no loads, no loop) — the small-scene form the shared-memory wavefront uses.
+constexpr int kParamPairs = kBruteParamPairs;
+struct BruteParam { float4 e[5 * kParamPairs]; };
+template <class G>
+PT_DEV void closest_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
+    best_t = FLT_MAX; best_id = -1;
+    float tmax = __int_as_float(0x7f800000);
+#pragma unroll
+    for (int e = 0; e < kParamPairs; ++e) {
+        if (e >= (int)g.n_pairs) break;
+        pair_closest(bp.e[5 * e], bp.e[5 * e + 1], bp.e[5 * e + 2], bp.e[5 * e + 3], bp.e[5 * e + 4], ro, rd, t_min, tmax, best_id);
+    }
+    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
+        single_closest(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 4], ro, rd, t_min, tmax, best_id);
+    if (best_id >= 0) best_t = tmax;
+}
+template <class G>
+PT_DEV bool any_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd, float t_min, float t_max) {
+    bool occluded = false;
+#pragma unroll
+    for (int e = 0; e < kParamPairs; ++e) {
+        if (e >= (int)g.n_pairs) break;
+        occluded |= pair_any(bp.e[5 * e], bp.e[5 * e + 1], bp.e[5 * e + 2], bp.e[5 * e + 3], bp.e[5 * e + 4], ro, rd, t_min, t_max);
+    }
+    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
+        occluded |= hit_prim(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], ro, rd, t_min, t_max) >= 0.0f;
+    return occluded;
+}
+
 // Closest hit.  Winner = smallest t in [t_min, inf); equal t -> higher object index (world.rs:281-287 scans
 // in index order with an inclusive t_max, so a later object replaces an earlier one on a tie).
 template <bool SMEM, bool BRUTE, class G>
@@ -107,24 +159,10 @@ PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, fl
         if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
     };
     if (BRUTE && SMEM && g.brute) {
-        // Scan table in ascending object order; consecutive triangles come as packed pairs (pt_math.cuh: hit_triangle2).  Both
-        // tests of a pair see the t_max in force before the pair and the updates re-check the inclusive bound in index order:
-        // the same winner as the sequential scan of world.rs:281-287 (ties go to the later object).
-        for (uint32_t e = 0; e < g.n_brute; ++e) {
-            const float4 A = g.brute[5 * e], B = g.brute[5 * e + 1], C = g.brute[5 * e + 2], E = g.brute[5 * e + 4];
-            const int ida = __float_as_int(E.z), idb = __float_as_int(E.w);
-            if (idb >= 0) {
-                const float4 D = g.brute[5 * e + 3];
-                bool oka, okb;
-                float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
-                                         pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax, oka, okb);
-                if (oka) { tmax = t.x; best_id = ida; }
-                if (okb & (t.y <= tmax)) { tmax = t.y; best_id = idb; }
-            } else {
-                float t = hit_prim(A, B, C, ro, rd, t_min, tmax);
-                if (t >= 0.0f && t <= tmax) { tmax = t; best_id = ida; }
-            }
-        }
+        for (uint32_t e = 0; e < g.n_pairs; ++e)
+            pair_closest(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 3], g.brute[5 * e + 4], ro, rd, t_min, tmax, best_id);
+        for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
+            single_closest(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 4], ro, rd, t_min, tmax, best_id);
     } else if (BRUTE) {
         for (int id = 0; id < (int)n_objects; ++id) test(id);
     } else {
@@ -155,18 +193,10 @@ template <bool SMEM, bool BRUTE, class G>
 PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float t_min, float t_max) {
     if (BRUTE && SMEM && g.brute) {
         bool occluded = false;
-        for (uint32_t e = 0; e < g.n_brute; ++e) {
-            const float4 A = g.brute[5 * e], B = g.brute[5 * e + 1], C = g.brute[5 * e + 2], E = g.brute[5 * e + 4];
-            if (__float_as_int(E.w) >= 0) {
-                const float4 D = g.brute[5 * e + 3];
-                bool oka, okb;
-                hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
-                              pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, t_max, oka, okb);
-                occluded |= oka | okb;
-            } else {
-                occluded |= hit_prim(A, B, C, ro, rd, t_min, t_max) >= 0.0f;
-            }
-        }
+        for (uint32_t e = 0; e < g.n_pairs; ++e)
+            occluded |= pair_any(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 3], g.brute[5 * e + 4], ro, rd, t_min, t_max);
+        for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
+            occluded |= hit_prim(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], ro, rd, t_min, t_max) >= 0.0f;
         return occluded;
     }
     if (BRUTE) {
@@ -348,7 +378,7 @@ inline SceneView make_scene_view(const SceneDev& d) {
     SceneView v;
     v.prims = d.prims; v.mats = d.mats; v.light_ids = d.light_ids; v.nodes = d.nodes;
     v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
-    v.brute = d.brute; v.n_brute = d.n_brute;
+    v.brute = d.brute; v.n_brute = d.n_brute; v.n_pairs = d.n_pairs;
     return v;
 }
 inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {

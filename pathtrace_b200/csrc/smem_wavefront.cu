@@ -17,6 +17,9 @@
 #include <cstdio>
 #include <vector>
 
+#include <cstdlib>
+#include <cstring>
+
 #include "pt_wave.cuh"
 
 using namespace ptw;
@@ -59,8 +62,12 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
     return b;
 }
 
-template <bool BRUTE, bool PROF>
-__global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out) {
+// MODE 0: LBVH from shared memory; 1: scan table from shared memory; 2: its triangle pairs from the kernel parameter `bp`
+// (constant bank, unrolled) and only the unpaired primitives from shared memory.
+template <int MODE, bool PROF>
+__global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
+                                                                           const __grid_constant__ BruteParam bp) {
+    constexpr bool BRUTE = MODE != 0;
     constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NTILES = kSwSlots / 32;
     extern __shared__ float4 smem[];
     float4* s_ro = smem;
@@ -98,8 +105,16 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     Geo<true, 4> g; g.nodes = s_nodes; g.prims = s_prims;
     if (BRUTE && s.brute) {
         for (uint32_t i = tid; i < s.n_brute * 5; i += kSwBlock) s_brute[i] = __ldg(s.brute + i);
-        g.brute = s_brute; g.n_brute = s.n_brute;
+        g.brute = s_brute; g.n_brute = s.n_brute; g.n_pairs = s.n_pairs;
     }
+    auto trace_closest = [&](float3 ro, float3 rd, float& t, int& id) {
+        if (MODE == 2) closest_hit_param(bp, g, ro, rd, f.t_min, t, id);
+        else closest_hit<true, BRUTE>(g, s.n_objects, ro, rd, f.t_min, t, id);
+    };
+    auto trace_any = [&](float3 ro, float3 rd, float t_max) -> bool {
+        if (MODE == 2) return any_hit_param(bp, g, ro, rd, f.t_min, t_max);
+        return any_hit<true, BRUTE>(g, s.n_objects, ro, rd, f.t_min, t_max);
+    };
     const SceneShared sc{s_prims, s_mats, s_lights, s.n_lights};
 
     // ---- K1: initial fill of this CTA's slots from its work range
@@ -133,7 +148,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             if (META_ALIVE(m)) {
                 float4 ro = s_ro[j], rd = s_rd[j];
                 float t; int id;
-                closest_hit<true, BRUTE>(g, s.n_objects, v3(ro), v3(rd), f.t_min, t, id);
+                trace_closest(v3(ro), v3(rd), t, id);
                 s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
                 if (id < 0) c = CLS_MISS;
                 else {
@@ -210,7 +225,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
 #if PT_SW_INLINE_SHADOW
             // K5 inline: the shadow ray starts at the hit point (the new ray origin) and is traced by the lane that shaded
             // the vertex; unoccluded contributions go straight to the pixel (rendering.rs:62-80).
-            if (emit_shadow && !any_hit<true, BRUTE>(g, s.n_objects, p_hit, sh_d, f.t_min, sh_tmax))
+            if (emit_shadow && !trace_any(p_hit, sh_d, sh_tmax))
                 atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
             c_shadow += emit_shadow ? 1u : 0u;
 #else
@@ -267,7 +282,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             float4 d = s_shd[e], c = s_shc[e];
             uint32_t j = __float_as_uint(c.w);
             float4 o = s_ro[j];
-            if (!any_hit<true, BRUTE>(g, s.n_objects, v3(o), v3(d), f.t_min, d.w))
+            if (!trace_any(v3(o), v3(d), d.w))
                 atomicAdd(f.accum + META_PIXEL(s_meta[j]), make_float4(c.x, c.y, c.z, 0.f));   // rendering.rs:70-80
         }
 #endif
@@ -317,9 +332,24 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kSwBlock, smem));
         return PT_OK;
     };
+    // brute force over a table whose pairs all fit the kernel parameter: MODE 2 (env PT_SW_NO_PARAM=1 keeps MODE 1, for A/B runs)
+    static const bool no_param = getenv("PT_SW_NO_PARAM") != nullptr;
+    const int mode = !brute ? 0 : (scene.brute && scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty() && !no_param) ? 2 : 1;
+    BruteParam bp;
+    memset(&bp, 0, sizeof(bp));
+    if (mode == 2) memcpy(bp.e, scene.brute_host.data(), sizeof(float4) * scene.brute_host.size());
     int occ = 0, rc;
-    if (brute) rc = profile ? pick(k_smem_wavefront<true, true>, occ) : pick(k_smem_wavefront<true, false>, occ);
-    else rc = profile ? pick(k_smem_wavefront<false, true>, occ) : pick(k_smem_wavefront<false, false>, occ);
+    auto with_kernel = [&](auto&& fn) -> int {
+        switch (mode * 2 + (profile ? 1 : 0)) {
+            case 0: return fn(k_smem_wavefront<0, false>);
+            case 1: return fn(k_smem_wavefront<0, true>);
+            case 2: return fn(k_smem_wavefront<1, false>);
+            case 3: return fn(k_smem_wavefront<1, true>);
+            case 4: return fn(k_smem_wavefront<2, false>);
+            default: return fn(k_smem_wavefront<2, true>);
+        }
+    };
+    rc = with_kernel([&](auto kernel) { return pick(kernel, occ); });
     if (rc) return rc;
     if (occ < 1) { ctx->err = "smem wavefront: kernel does not fit on an SM"; return PT_ERR_CUDA; }
 
@@ -348,13 +378,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         while (ctx->prof_events.size() < 2) { cudaEvent_t e; PT_CUDA_CHECK(ctx, cudaEventCreate(&e)); ctx->prof_events.push_back(e); }
         PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[0], st));
     }
-    if (brute) {
-        if (profile) k_smem_wavefront<true, true><<<grid, kSwBlock, smem, st>>>(sv, f, out);
-        else k_smem_wavefront<true, false><<<grid, kSwBlock, smem, st>>>(sv, f, out);
-    } else {
-        if (profile) k_smem_wavefront<false, true><<<grid, kSwBlock, smem, st>>>(sv, f, out);
-        else k_smem_wavefront<false, false><<<grid, kSwBlock, smem, st>>>(sv, f, out);
-    }
+    with_kernel([&](auto kernel) { kernel<<<grid, kSwBlock, smem, st>>>(sv, f, out, bp); return PT_OK; });
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     if (profile) PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[1], st));
     if (stats) {

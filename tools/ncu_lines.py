@@ -78,6 +78,22 @@ def main():
         for i in stall_cols:
             if r[i] not in ("", "0"):
                 stalls[w][hdr[i]] += int(r[i])
+    if os.environ.get("OPS"):        # OPS=1: executed-instruction histogram by opcode (and by opcode within the top lines)
+        hs = hdr.index("Source")
+        ops, ops_line = defaultdict(int), defaultdict(lambda: defaultdict(int))
+        for r in body:
+            toks = [t for t in r[hs].split() if not t.startswith("@")]
+            op = toks[0].rstrip(";") if toks else "?"
+            op = ".".join(op.split(".")[:2]) if op.startswith(("LDS", "STS", "MUFU", "ATOMS", "RED", "LDG", "STG")) else op.split(".")[0]
+            ops[op] += int(r[ci])
+            ops_line[off2line.get(int(r[0], 16) - base, "?")][op] += int(r[ci])
+        tot = sum(ops.values())
+        print(f"{tot} warp instructions")
+        for op, v in sorted(ops.items(), key=lambda kv: -kv[1])[:top]:
+            print(f"  {op:14s} {100 * v / tot:6.2f} %")
+        for w in sorted(inst, key=lambda k: -inst[k])[:int(os.environ.get("OPS_LINES", "12"))]:
+            print(f"{w:28s} {100 * inst[w] / tot:6.2f} %  " + " ".join(f"{o}={100 * v / tot:.2f}" for o, v in sorted(ops_line[w].items(), key=lambda kv: -kv[1])[:8]))
+        return
     ti, ts = sum(inst.values()), sum(samp.values())
     print(f"kernel {kre}: {ti} warp instructions, {ts} samples, avg threads {sum(thr.values()) / max(ti, 1):.2f}")
     print(f"{'line':28s} {'inst%':>6s} {'samp%':>6s} {'thr':>5s}  top stalls")
