@@ -1,24 +1,24 @@
 // smem_wavefront.cu — the wavefront sample loop with its queues in SHARED memory (sm_100a, 227 KB per SM).
 //
 // Same stages as wavefront.cu (K1 generate, K3 closest hit, K4/K6/K7 shade, K5 shadow, K8 accumulate), same device
-// functions (pt_wave.cuh), same counter-based RNG — but when the whole scene (primitives, materials, LBVH) fits in a few
-// KB of shared memory, nothing about a path needs to leave the SM between bounces.  Each CTA owns kSwSlots path slots
-// whose SoA float4 queues (ray origin|eta, direction|pdf, throughput, hit, meta, shadow queue) live in shared memory,
-// owns a contiguous range of the (pixel, sample) work list, and runs the wavefront to completion on its own:
+// functions (pt_wave.cuh), same counter-based RNG — but when the whole scene (primitives, materials, LBVH or scan table) fits
+// in a few KB of shared memory, nothing about a path needs to leave the SM between bounces.  Each CTA owns kSwSlots path
+// slots whose SoA float4 state (ray origin|eta, direction|pdf, throughput, hit, meta) lives in shared memory, owns a
+// contiguous range of the (pixel, sample) work list, and runs the wavefront to completion on its own:
 //
-//   loop:  T  closest hit of every live slot, slot order (coherent straight-line code)      world.rs:270-290
-//          S  counting sort of the slots by hit class (mirror / diffuse / emissive / miss)  warp ballot + popc
-//          A  warps pull 32-slot tiles of the sorted list: shade_vertex(), shadow-queue compaction (ballot/popc + one
-//             shared atomic per warp), accumulate finished paths, re-seed their slots       rendering.rs:34-142
-//          H  any-hit over the compacted shadow queue, accumulate unoccluded contributions  rendering.rs:62-65
+//   loop:  T  work list = [slots whose path continues ... | ... slots to re-seed]: the re-seeded ones get a camera ray
+//             (K1, camera.rs:139-147) from the CTA's work range, then every entry finds its closest hit (world.rs:270-290)
+//          S  counting sort of the entries by hit class (mirror / diffuse / emissive / miss), match + popc per warp
+//          A  warps pull 32-slot tiles of the sorted list: shade_vertex() (rendering.rs:34-142), the vertex's shadow ray
+//             traced in line (rendering.rs:62-80), finished paths accumulated (world.rs:296-313); each slot is appended to
+//             the front (continues) or the back (re-seed) of the next work list, so camera-ray generation is dense too
 //
 // HBM traffic is what the algorithm needs: one float4 atomic add per finished path / unoccluded shadow ray.
 // CTAs never communicate, so one launch renders the frame: no per-bounce launches, no host round trips.
 #include <cstdio>
-#include <vector>
-
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "pt_wave.cuh"
 
@@ -37,11 +37,6 @@ namespace {
 #ifndef PT_SW_MIN_BLOCKS
 #define PT_SW_MIN_BLOCKS 1
 #endif
-// 1: a vertex traces its own shadow ray right after it is shaded (no shadow queue: 32 B per slot less shared memory, one
-// barrier less, no partially filled last round).  0: shadow rays go through a compacted shared-memory queue and a phase H.
-#ifndef PT_SW_INLINE_SHADOW
-#define PT_SW_INLINE_SHADOW 1
-#endif
 constexpr int kSwBlock = PT_SW_BLOCK, kSwSpt = PT_SW_SPT, kSwSlots = kSwBlock * kSwSpt, kSwMinBlocks = PT_SW_MIN_BLOCKS;
 
 struct SwOut {
@@ -53,11 +48,11 @@ struct SwOut {
 // Bytes of dynamic shared memory for a scene (must match the carve-up in the kernel).
 size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bool brute) {
     size_t b = 0;
-    b += 16 * (size_t)kSwSlots * (PT_SW_INLINE_SHADOW ? 3 : 5);   // ro, rd, beta (, shadow d, shadow c)
+    b += 16 * (size_t)kSwSlots * 3;                 // ro, rd, beta
     b += 8 * (size_t)kSwSlots * 2;                  // hit, meta
     b += 16 * ((brute ? 0 : (size_t)n_nodes * 4) + (size_t)n_objects * 4 + (size_t)n_objects * 2);
     b += 4 * (((size_t)n_lights + 3) & ~size_t(3));
-    b += 2 * (((size_t)kSwSlots + 7) & ~size_t(7));  // sorted order
+    b += 2 * 2 * (((size_t)kSwSlots + 7) & ~size_t(7));   // sorted order, next work list
     b += brute ? 16 * 5 * (size_t)n_objects : 0;    // brute-force scan table (at most one entry per object)
     return b;
 }
@@ -68,32 +63,27 @@ template <int MODE, bool PROF>
 __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
                                                                            const __grid_constant__ BruteParam bp) {
     constexpr bool BRUTE = MODE != 0;
-    constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NTILES = kSwSlots / 32;
+    constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NGRP = SPT * NW;
     extern __shared__ float4 smem[];
     float4* s_ro = smem;
     float4* s_rd = s_ro + kSwSlots;
     float4* s_beta = s_rd + kSwSlots;
-#if PT_SW_INLINE_SHADOW
     uint2* s_hit = reinterpret_cast<uint2*>(s_beta + kSwSlots);
-#else
-    float4* s_shd = s_beta + kSwSlots;                 // shadow queue: direction.xyz, t_max
-    float4* s_shc = s_shd + kSwSlots;                  // contribution.rgb, slot bits
-    uint2* s_hit = reinterpret_cast<uint2*>(s_shc + kSwSlots);
-#endif
     uint2* s_meta = s_hit + kSwSlots;
     float4* s_nodes = reinterpret_cast<float4*>(s_meta + kSwSlots);
     float4* s_prims = s_nodes + (BRUTE ? 0 : s.n_nodes * 4);
     float4* s_mats = s_prims + s.n_objects * 4;
     uint32_t* s_lights = reinterpret_cast<uint32_t*>(s_mats + s.n_objects * 2);
-    uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));
-    float4* s_brute = reinterpret_cast<float4*>(s_order + ((kSwSlots + 7) & ~7));
-    __shared__ uint16_t s_cls_cnt[CLS_COUNT][SPT * NW];
+    uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));   // class-sorted slots (phase A reads)
+    uint16_t* s_list = s_order + ((kSwSlots + 7) & ~7);                                     // next work list (phase A writes)
+    float4* s_brute = reinterpret_cast<float4*>(s_list + ((kSwSlots + 7) & ~7));
+    __shared__ uint16_t s_cls_cnt[CLS_COUNT][NGRP];
     __shared__ uint32_t s_cls_total[CLS_COUNT];
     __shared__ unsigned long long s_next;      // this CTA's next work item
-    __shared__ uint32_t s_shadow, s_tile, s_alive;
-    __shared__ unsigned long long s_clk[4];    // PROF: t_prev, T+S, A, H
+    __shared__ uint32_t s_ncont, s_nregen, s_tile;
+    __shared__ unsigned long long s_clk[3];    // PROF: t_prev, T+S, A
 
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
     const bool mis = f.strategy == PT_STRATEGY_MIS;
     const uint64_t work_lo = (uint64_t)blockIdx.x * f.chunk, work_hi = work_lo + f.chunk < f.total_work ? work_lo + f.chunk : f.total_work;
 
@@ -117,36 +107,42 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     };
     const SceneShared sc{s_prims, s_mats, s_lights, s.n_lights};
 
-    // ---- K1: initial fill of this CTA's slots from its work range
-#pragma unroll
-    for (int k = 0; k < SPT; ++k) {
-        uint32_t j = k * kSwBlock + tid;
-        uint64_t w = work_lo + j;
-        if (w < work_hi) {
-            float4 ro, rd; uint2 m;
-            make_primary(f, w, ro, rd, m);
-            s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
-        } else {
-            s_meta[j] = make_uint2(0u, 0u);
-        }
-    }
+    // ---- the first work list re-seeds every slot
+    for (uint32_t i = tid; i < (uint32_t)kSwSlots; i += kSwBlock) s_list[i] = (uint16_t)i;
     if (tid == 0) {
-        s_next = work_lo + kSwSlots;
-        if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = s_clk[3] = 0; }
+        s_next = work_lo; s_ncont = 0; s_nregen = kSwSlots; s_tile = 0;
+        if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = 0; }
     }
     uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // per-lane counters, reduced once at the end
     __syncthreads();
 
     while (true) {
-        // ---- phase T: closest hit in slot order + classification
-        uint32_t cls[SPT], rank[SPT];
+        // ---- phase T: entries [0, n_cont) continue a path; the last n_regen entries take new work items base, base+1, ...
+        // from the back (entry kSwSlots-1 first) while the CTA's range lasts.  Entries in between, and re-seed entries past
+        // the end of the range, are dead: they sort last and phase A never touches them.
+        const uint32_t n_cont = s_ncont, n_regen = s_nregen;
+        const uint64_t base = s_next;
+        const uint64_t avail = work_hi > base ? work_hi - base : 0;
+        const uint32_t n_new = avail < n_regen ? (uint32_t)avail : n_regen;
+        if (n_cont + n_new == 0) break;                              // uniform: nothing left in this CTA
+        if (lane < CLS_COUNT * SPT) s_cls_cnt[lane / SPT][(lane % SPT) * NW + warp] = 0;
+        __syncwarp();
+        uint32_t cls[SPT], rank[SPT], slot[SPT];
 #pragma unroll
         for (int k = 0; k < SPT; ++k) {
-            uint32_t j = k * kSwBlock + tid;
-            uint2 m = s_meta[j];
-            uint32_t c = CLS_DEAD;
-            if (META_ALIVE(m)) {
-                float4 ro = s_ro[j], rd = s_rd[j];
+            const uint32_t e = k * kSwBlock + tid;
+            uint32_t c = CLS_DEAD, j = 0;
+            const bool cont = e < n_cont, seed = e >= kSwSlots - n_new;
+            if (cont || seed) {
+                j = s_list[e];
+                float4 ro, rd;
+                if (seed) {
+                    uint2 m;
+                    make_primary(f, base + (kSwSlots - 1 - e), ro, rd, m);
+                    s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
+                } else {
+                    ro = s_ro[j]; rd = s_rd[j];
+                }
                 float t; int id;
                 trace_closest(v3(ro), v3(rd), t, id);
                 s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
@@ -156,143 +152,93 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                     c = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
                 }
             }
-            cls[k] = c; rank[k] = 0;
-#pragma unroll
-            for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) {
-                uint32_t b = __ballot_sync(0xffffffffu, c == cc);
-                if (lane == 0) s_cls_cnt[cc][k * NW + warp] = (uint16_t)__popc(b);
-                if (c == cc) rank[k] = __popc(b & ((1u << lane) - 1));
-            }
+            const uint32_t same = __match_any_sync(0xffffffffu, c);  // lanes of this group in the same class
+            cls[k] = c; slot[k] = j; rank[k] = __popc(same & lt_mask);
+            if (rank[k] == 0) s_cls_cnt[c][k * NW + warp] = (uint16_t)__popc(same);
         }
-        if (tid == 0) { s_shadow = 0; s_tile = 0; s_alive = 0; }
         __syncthreads();
-        // ---- phase S: counting sort by class.  Warp cc scans the SPT*NW group counts of class cc (exclusive, in place);
+        if (tid == 0) { s_next = base + n_new; s_ncont = 0; s_nregen = 0; s_tile = 0; }
+        // ---- phase S: counting sort by class.  Warp cc scans the NGRP group counts of class cc (exclusive, in place);
         // the class bases are the running sum of the five totals.
         for (uint32_t cc = warp; cc < CLS_COUNT; cc += NW) {
-            constexpr uint32_t N = SPT * NW;
             uint16_t* row = s_cls_cnt[cc];
             uint32_t run = 0;
-            for (uint32_t k0 = 0; k0 < N; k0 += 32) {
+            for (uint32_t k0 = 0; k0 < NGRP; k0 += 32) {
                 uint32_t k = k0 + lane;
-                uint32_t v = k < N ? row[k] : 0, x = v;
+                uint32_t v = k < NGRP ? row[k] : 0, x = v;
                 for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-                if (k < N) row[k] = (uint16_t)(run + x - v);
+                if (k < NGRP) row[k] = (uint16_t)(run + x - v);
                 run += __shfl_sync(0xffffffffu, x, 31);
             }
             if (lane == 0) s_cls_total[cc] = run;
         }
         __syncthreads();
+        uint32_t n_live;
         {
             uint32_t start[CLS_COUNT], acc = 0;
 #pragma unroll
             for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) { start[cc] = acc; acc += s_cls_total[cc]; }
+            n_live = start[CLS_DEAD];                                // CLS_DEAD is the last class
 #pragma unroll
             for (int k = 0; k < SPT; ++k) {
                 uint32_t st = 0;
 #pragma unroll
                 for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) st = cls[k] == cc ? start[cc] : st;
-                s_order[st + s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)(k * kSwBlock + tid);
+                s_order[st + s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)slot[k];
             }
         }
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[1] += t - s_clk[0]; s_clk[0] = t; }
 
-        // ---- phase A: dynamic tiles of the class-sorted slot list
-        uint32_t n_alive = 0;
+        // ---- phase A: dynamic tiles of the class-sorted list
         while (true) {
             uint32_t tile = 0;
             if (lane == 0) tile = atomicAdd(&s_tile, 1u);
             tile = __shfl_sync(0xffffffffu, tile, 0);
-            if (tile >= NTILES) break;
-            const uint32_t j = s_order[tile * 32 + lane];
+            if (tile * 32 >= n_live) break;
+            const bool alive = tile * 32 + lane < n_live;
+            const uint32_t j = alive ? s_order[tile * 32 + lane] : 0u;
             const uint2 meta = s_meta[j];
-            bool alive = META_ALIVE(meta);
-            if (!__any_sync(0xffffffffu, alive)) break;          // sorted: dead slots are last
-            bool finished = false, emit_shadow = false, add_L = false, vertex = false;
-            float3 Ladd = v3(0.f, 0.f, 0.f), sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f);
+            bool finished = false, emit_shadow = false;
+            float3 sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f), p_hit = v3(0.f, 0.f, 0.f);
             float sh_tmax = 0.f;
-            float3 p_hit = v3(0.f, 0.f, 0.f);
             if (alive) {
                 VertexOut vo = shade_vertex(sc, f, mis, s_ro[j], s_rd[j], v3(s_beta[j]), s_hit[j], meta);
-                p_hit = v3(vo.new_ro);
-                finished = vo.finished; add_L = vo.add_L; Ladd = vo.Ladd; vertex = vo.vertex;
-                if (!vo.finished) {
+                finished = vo.finished;
+                c_vertex += vo.vertex ? 1u : 0u;
+                if (vo.finished) {
+                    // K8 accumulate (world.rs:296-313)
+                    if (vo.add_L) atomicAdd(f.accum + META_PIXEL(meta), make_float4(vo.Ladd.x, vo.Ladd.y, vo.Ladd.z, 0.f));
+                } else {
+                    p_hit = v3(vo.new_ro);
                     emit_shadow = vo.emit_shadow; sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
                     s_ro[j] = vo.new_ro; s_rd[j] = vo.new_rd; s_meta[j] = vo.new_meta;
                     s_beta[j] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
+                    ++c_scatter;
                 }
             }
-#if PT_SW_INLINE_SHADOW
-            // K5 inline: the shadow ray starts at the hit point (the new ray origin) and is traced by the lane that shaded
+            // K5 in line: the shadow ray starts at the hit point (the new ray origin) and is traced by the lane that shaded
             // the vertex; unoccluded contributions go straight to the pixel (rendering.rs:62-80).
-            if (emit_shadow && !trace_any(p_hit, sh_d, sh_tmax))
-                atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
-            c_shadow += emit_shadow ? 1u : 0u;
-#else
-            // shadow queue compaction: warp ballot/popc + one shared-memory atomic per warp.  The ray starts at the new
-            // origin of slot j (the hit point), so an entry is (direction, t_max, contribution, slot).
-            {
-                uint32_t bal = __ballot_sync(0xffffffffu, emit_shadow);
-                uint32_t sbase = 0;
-                if (lane == 0 && bal) sbase = atomicAdd(&s_shadow, (uint32_t)__popc(bal));
-                sbase = __shfl_sync(0xffffffffu, sbase, 0);
-                if (emit_shadow) {
-                    uint32_t e = sbase + __popc(bal & ((1u << lane) - 1));
-                    s_shd[e] = make_float4(sh_d.x, sh_d.y, sh_d.z, sh_tmax);
-                    s_shc[e] = make_float4(sh_c.x, sh_c.y, sh_c.z, __uint_as_float(j));
-                }
-                c_shadow += emit_shadow ? 1u : 0u;
+            if (emit_shadow) {
+                ++c_shadow;
+                if (!trace_any(p_hit, sh_d, sh_tmax)) atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
             }
-#endif
-            c_vertex += vertex ? 1u : 0u;
-            c_scatter += (alive && !finished) ? 1u : 0u;
-            // K8 accumulate (world.rs:296-313) + regeneration from this CTA's private work range
+            // next work list: continuing slots from the front, slots to re-seed from the back
             {
-                uint32_t bal = __ballot_sync(0xffffffffu, finished);
-                unsigned long long wbase = 0;
-                if (lane == 0 && bal) wbase = atomicAdd(&s_next, (unsigned long long)__popc(bal));
-                wbase = __shfl_sync(0xffffffffu, wbase, 0);
-                if (finished) {
-                    if (add_L) atomicAdd(f.accum + META_PIXEL(meta), make_float4(Ladd.x, Ladd.y, Ladd.z, 0.f));
-                    uint64_t w = wbase + __popc(bal & ((1u << lane) - 1));
-                    if (w < work_hi) {
-                        float4 ro, rd; uint2 m;
-                        make_primary(f, w, ro, rd, m);
-                        s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
-                    } else {
-                        s_meta[j] = make_uint2(0u, 0u);
-                        alive = false;
-                    }
-                }
-                n_alive += alive ? 1u : 0u;
+                const uint32_t fin = __ballot_sync(0xffffffffu, alive && finished), con = __ballot_sync(0xffffffffu, alive && !finished);
+                uint32_t b = 0;
+                if (lane == 0 && fin) b = atomicAdd(&s_nregen, (uint32_t)__popc(fin));
+                if (lane == 1 && con) b = atomicAdd(&s_ncont, (uint32_t)__popc(con));
+                const uint32_t bfin = __shfl_sync(0xffffffffu, b, 0), bcon = __shfl_sync(0xffffffffu, b, 1);
+                if (alive) s_list[finished ? kSwSlots - 1 - (bfin + __popc(fin & lt_mask)) : bcon + __popc(con & lt_mask)] = (uint16_t)j;
             }
         }
-        n_alive = __reduce_add_sync(0xffffffffu, n_alive);
-        if (lane == 0 && n_alive) atomicAdd(&s_alive, n_alive);
-        __syncthreads();
-        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
-        const uint32_t alive_now = s_alive;
-#if !PT_SW_INLINE_SHADOW
-        const uint32_t n_sh = s_shadow;
-#endif
-
-#if !PT_SW_INLINE_SHADOW
-        // ---- phase H: any-hit over the compacted shadow queue (dense: every warp is full except the last)
-        for (uint32_t e = tid; e < n_sh; e += kSwBlock) {
-            float4 d = s_shd[e], c = s_shc[e];
-            uint32_t j = __float_as_uint(c.w);
-            float4 o = s_ro[j];
-            if (!trace_any(v3(o), v3(d), d.w))
-                atomicAdd(f.accum + META_PIXEL(s_meta[j]), make_float4(c.x, c.y, c.z, 0.f));   // rendering.rs:70-80
-        }
-#endif
         ++iters;
         __syncthreads();
-        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[3] += t - s_clk[0]; s_clk[0] = t; }
-        if (alive_now == 0) break;
+        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
     }
 
-    // ---- bookkeeping: lane 0 of every warp holds its warp's counters
+    // ---- bookkeeping
     __shared__ uint32_t s_stats[3];
     if (tid < 3) s_stats[tid] = 0;
     __syncthreads();
@@ -300,11 +246,9 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     if (lane == 0) { atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex); }
     __syncthreads();
     if (tid == 0) {
-        unsigned long long handed = s_next < work_hi ? s_next : work_hi;
-        uint32_t primary = work_hi > work_lo ? (uint32_t)(handed - work_lo) : 0u;
-        out.block_stats[blockIdx.x] = make_uint4(primary, s_stats[0], s_stats[1], s_stats[2]);
+        out.block_stats[blockIdx.x] = make_uint4((uint32_t)(s_next - work_lo), s_stats[0], s_stats[1], s_stats[2]);
         out.block_iters[blockIdx.x] = iters;
-        if (PROF) { out.block_clk[3 * blockIdx.x] = s_clk[1]; out.block_clk[3 * blockIdx.x + 1] = s_clk[2]; out.block_clk[3 * blockIdx.x + 2] = s_clk[3]; }
+        if (PROF) { out.block_clk[3 * blockIdx.x] = s_clk[1]; out.block_clk[3 * blockIdx.x + 1] = s_clk[2]; out.block_clk[3 * blockIdx.x + 2] = 0; }
     }
 }
 
