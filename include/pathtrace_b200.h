@@ -80,7 +80,7 @@ typedef struct {
     float ms_kernel[5];         /* PT_FLAG_PROFILE only: summed CUDA-event time per kernel class (PT_K_*) */
     uint32_t n_kernel[5];       /* launches per kernel class */
     uint32_t path_pool;         /* pool size actually used */
-    float phase_share[3];       /* PT_FLAG_PROFILE, shared-memory wavefront: share of CTA cycles in closest-hit+sort, shade, shadow */
+    float phase_share[3];       /* PT_FLAG_PROFILE, shared-memory wavefront: share of warp cycles in closest-hit items, shading (+ shadow ray) items, waiting */
 } pt_stats;
 
 typedef struct pt_context pt_context;

@@ -44,7 +44,7 @@ class pt_stats(C.Structure):
         d = {k: getattr(self, k) for k, _ in self._fields_}
         d["ms_kernel"] = dict(zip(KERNEL_CLASSES, list(self.ms_kernel)))
         d["n_kernel"] = dict(zip(KERNEL_CLASSES, list(self.n_kernel)))
-        d["phase_share"] = dict(zip(("closest_hit", "shade", "shadow"), list(self.phase_share)))
+        d["phase_share"] = dict(zip(("closest_hit", "shade", "wait"), list(self.phase_share)))
         return d
 
 
