@@ -160,8 +160,13 @@ PT_DEV float3 orennayar_f(const Mat& m, float3 rd, float3 o, float3 n) {
     float si = sqrtf(fmaxf(1.0f - ci * ci, 0.0f)), so = sqrtf(fmaxf(1.0f - co * co, 0.0f));
     float3 tg, bt;
     tangent_frame(n, tg, bt);
-    float phi_i = atan2f(dot(i, bt), dot(i, tg)), phi_o = atan2f(dot(o, bt), dot(o, tg));
-    float cpd = fmaxf(cosf(phi_i - phi_o), 0.0f);
+    // cos(phi_i - phi_o) of material.rs:244-249 without the two atan2 and the cosine: with (x, y) = the tangent-plane
+    // coordinates, cos(phi_i - phi_o) = (xi xo + yi yo) / (|pi| |po|); a zero projection has phi = atan2(0, 0) = 0.
+    float xi = dot(i, tg), yi = dot(i, bt), xo = dot(o, tg), yo = dot(o, bt);
+    float ri2 = xi * xi + yi * yi, ro2 = xo * xo + yo * yo;
+    if (ri2 == 0.0f) { xi = 1.0f; yi = 0.0f; ri2 = 1.0f; }
+    if (ro2 == 0.0f) { xo = 1.0f; yo = 0.0f; ro2 = 1.0f; }
+    float cpd = fmaxf((xi * xo + yi * yo) * rsqrtf(ri2 * ro2), 0.0f);
     float sin_alpha, tan_beta;
     if (ci > co) { tan_beta = ci > 1e-6f ? si / ci : 0.0f; sin_alpha = so; }
     else         { tan_beta = co > 1e-6f ? so / co : 0.0f; sin_alpha = si; }

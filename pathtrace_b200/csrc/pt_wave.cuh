@@ -116,15 +116,20 @@ PT_DEV bool pair_any(float4 A, float4 B, float4 C, float4 D, float4 E, float3 ro
                   pk(E.x, E.y), ro, rd, t_min, t_max, oka, okb);
     return oka | okb;
 }
-// The first kParamPairs pairs of the table can also travel as a kernel parameter: the unrolled scan then takes its triangle
-// operands straight from the constant bank (no loads, no loop) — the small-scene form the shared-memory wavefront uses.
+// The first kParamPairs pairs of the table can also travel as a kernel parameter: the scan then takes its triangle operands
+// from the constant bank through uniform registers (no shared-memory loads, no vector registers) — the small-scene form the
+// shared-memory wavefront uses.  The loops stay rolled: the instruction cache is 32 KB and every warp of the CTA runs them.
 constexpr int kParamPairs = kBruteParamPairs;
 struct BruteParam { float4 e[5 * kParamPairs]; };
 template <class G>
 PT_DEV void closest_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
     best_t = FLT_MAX; best_id = -1;
     float tmax = __int_as_float(0x7f800000);
+#if PT_ROLL_CLOSEST
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
     for (int e = 0; e < kParamPairs; ++e) {
         if (e >= (int)g.n_pairs) break;
         pair_closest(bp.e[5 * e], bp.e[5 * e + 1], bp.e[5 * e + 2], bp.e[5 * e + 3], bp.e[5 * e + 4], ro, rd, t_min, tmax, best_id);
@@ -136,7 +141,11 @@ PT_DEV void closest_hit_param(const BruteParam& bp, const G& g, float3 ro, float
 template <class G>
 PT_DEV bool any_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd, float t_min, float t_max) {
     bool occluded = false;
+#if PT_ROLL_ANY
+#pragma unroll 1
+#else
 #pragma unroll
+#endif
     for (int e = 0; e < kParamPairs; ++e) {
         if (e >= (int)g.n_pairs) break;
         occluded |= pair_any(bp.e[5 * e], bp.e[5 * e + 1], bp.e[5 * e + 2], bp.e[5 * e + 3], bp.e[5 * e + 4], ro, rd, t_min, t_max);

@@ -4,21 +4,14 @@
 // functions (pt_wave.cuh), same counter-based RNG — but when the whole scene (primitives, materials, LBVH or scan table) fits
 // in a few KB of shared memory, nothing about a path needs to leave the SM between bounces.  Each CTA owns kSwSlots path
 // slots whose SoA float4 state (ray origin|eta, direction|pdf, throughput, hit, meta) lives in shared memory, owns a
-// contiguous range of the (pixel, sample) work list, and runs the wavefront to completion on its own.
+// contiguous range of the (pixel, sample) work list, and runs the wavefront to completion on its own:
 //
-// The slots form two halves that alternate roles, so one barrier per phase is all the synchronisation there is:
-//
-//   phase p:  half p&1      T  its work list = [slots whose path continues ... | ... slots to re-seed]: re-seeded slots get a
-//                              camera ray (K1, camera.rs:139-147) from the CTA's work range, every entry finds its closest hit
-//                              (world.rs:270-290) and is appended to the list of its hit class (mirror / diffuse / emissive /
-//                              miss; match + popc + one shared atomic per class and warp)
-//             other half    A  32-slot tiles of the class lists the previous phase built: shade_vertex() (rendering.rs:34-142),
-//                              the vertex's shadow ray traced in line (rendering.rs:62-80), finished paths accumulated
-//                              (world.rs:296-313); each slot goes to the front (continues) or the back (re-seed) of the half's
-//                              next work list
-//
-// Warps pull T groups and A tiles of a phase from ONE counter, expensive items first: the FMA-bound intersection work and
-// the latency-bound shading overlap on the SM, and the tail before the barrier is one cheap item long.
+//   loop:  T  work list = [slots whose path continues ... | ... slots to re-seed]: the re-seeded ones get a camera ray
+//             (K1, camera.rs:139-147) from the CTA's work range, then every entry finds its closest hit (world.rs:270-290)
+//          S  counting sort of the entries by hit class (mirror / diffuse / emissive / miss), match + popc per warp
+//          A  warps pull 32-slot tiles of the sorted list: shade_vertex() (rendering.rs:34-142), the vertex's shadow ray
+//             traced in line (rendering.rs:62-80), finished paths accumulated (world.rs:296-313); each slot is appended to
+//             the front (continues) or the back (re-seed) of the next work list, so camera-ray generation is dense too
 //
 // HBM traffic is what the algorithm needs: one float4 atomic add per finished path / unoccluded shadow ray.
 // CTAs never communicate, so one launch renders the frame: no per-bounce launches, no host round trips.
@@ -33,30 +26,24 @@ using namespace ptw;
 
 namespace {
 
-// One CTA per SM.  3072 slots (two halves of 1536) fill the shared memory next to a small scene; the class lists of a half
-// are long enough that almost every 32-slot tile is full (measured: 512-slot windows lose ~12 % to partial tiles).  896
-// threads = 72 registers per thread: fewer, fatter warps beat 1024 threads at 64 registers (spills in the unrolled scan).
+// One CTA of 896 threads per SM owning 2688 slots: the class sort sees a window wide enough that almost every 32-slot tile
+// is a single class (measured: 512-slot windows lose ~12 % to mixed tiles), 3 rays per thread keep phase T balanced, and 72
+// registers per thread beat 1024 threads at 64 (4.32 vs 4.07 Gsamples/s: fewer spills around the unrolled scan).
 #ifndef PT_SW_BLOCK
 #define PT_SW_BLOCK 896
 #endif
-#ifndef PT_SW_SLOTS
-#define PT_SW_SLOTS 3072
+#ifndef PT_SW_SPT
+#define PT_SW_SPT 3
 #endif
-constexpr int kSwBlock = PT_SW_BLOCK, kSwSlots = PT_SW_SLOTS, kSwHalf = kSwSlots / 2;
-static_assert(kSwBlock % 32 == 0 && kSwHalf % 32 == 0 && kSwSlots <= 65536, "slot ids are 16-bit, halves are whole tiles");
+#ifndef PT_SW_MIN_BLOCKS
+#define PT_SW_MIN_BLOCKS 1
+#endif
+constexpr int kSwBlock = PT_SW_BLOCK, kSwSpt = PT_SW_SPT, kSwSlots = kSwBlock * kSwSpt, kSwMinBlocks = PT_SW_MIN_BLOCKS;
 
 struct SwOut {
     uint4* block_stats;       // per CTA: primary, shadow, scattered, vertices
-    uint32_t* block_iters;    // per CTA: phases it ran
-    unsigned long long* block_clk;   // per CTA (PROF only): warp cycles in T items, A items, waiting
-};
-
-// Counters of one phase.  Three of them rotate: phase p fills ring[p % 3], reads ring[(p - 1) % 3] and clears ring[(p + 1) % 3]
-// (last read at the start of phase p - 1), so no counter is ever reset while somebody may still read it.
-struct SwRing {
-    uint32_t cls[4];          // T: entries appended to each class list of the half it traced
-    uint32_t n_cont, n_regen; // A: entries appended to the front / the back of its half's next work list
-    uint32_t item, pad;       // work items handed out in this phase
+    uint32_t* block_iters;    // per CTA: wavefront iterations it ran
+    unsigned long long* block_clk;   // per CTA (PROF only): cycles in phases T+S, A, H
 };
 
 // Bytes of dynamic shared memory for a scene (must match the carve-up in the kernel).
@@ -66,7 +53,7 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
     b += 8 * (size_t)kSwSlots * 2;                  // hit, meta
     b += 16 * ((brute ? 0 : (size_t)n_nodes * 4) + (size_t)n_objects * 4 + (size_t)n_objects * 2);
     b += 4 * (((size_t)n_lights + 3) & ~size_t(3));
-    b += 2 * 3 * (size_t)kSwSlots;                  // per half: mirror|diffuse list, emissive|miss list, next work list
+    b += 2 * 2 * (((size_t)kSwSlots + 7) & ~size_t(7));   // sorted order, next work list
     b += brute ? 16 * 5 * (size_t)n_objects : 0;    // brute-force scan table (at most one entry per object)
     return b;
 }
@@ -74,10 +61,10 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
 // MODE 0: LBVH from shared memory; 1: scan table from shared memory; 2: its triangle pairs from the kernel parameter `bp`
 // (constant bank, unrolled) and only the unpaired primitives from shared memory.
 template <int MODE, bool PROF>
-__global__ void __launch_bounds__(kSwBlock, 1) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
-                                                                const __grid_constant__ BruteParam bp) {
+__global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
+                                                                           const __grid_constant__ BruteParam bp) {
     constexpr bool BRUTE = MODE != 0;
-    constexpr uint32_t H = kSwHalf;
+    constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NGRP = SPT * NW;
     extern __shared__ float4 smem[];
     float4* s_ro = smem;
     float4* s_rd = s_ro + kSwSlots;
@@ -88,15 +75,16 @@ __global__ void __launch_bounds__(kSwBlock, 1) k_smem_wavefront(SceneView s, con
     float4* s_prims = s_nodes + (BRUTE ? 0 : s.n_nodes * 4);
     float4* s_mats = s_prims + s.n_objects * 4;
     uint32_t* s_lights = reinterpret_cast<uint32_t*>(s_mats + s.n_objects * 2);
-    uint16_t* s_ord_a = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));   // [half][H]: mirror ->  <- diffuse
-    uint16_t* s_ord_b = s_ord_a + kSwSlots;                                                 // [half][H]: emissive ->  <- miss
-    uint16_t* s_list = s_ord_b + kSwSlots;                                                  // [half][H]: continue ->  <- re-seed
-    float4* s_brute = reinterpret_cast<float4*>(s_list + kSwSlots);
-    __shared__ SwRing s_ring[3];
-    __shared__ unsigned long long s_clk[3];    // PROF: warp cycles in T items, A items, total
-    __shared__ uint32_t s_stats[3];
+    uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));   // class-sorted slots (phase A reads)
+    uint16_t* s_list = s_order + ((kSwSlots + 7) & ~7);                                     // next work list (phase A writes)
+    float4* s_brute = reinterpret_cast<float4*>(s_list + ((kSwSlots + 7) & ~7));
+    __shared__ uint16_t s_cls_cnt[CLS_COUNT][NGRP];
+    __shared__ uint32_t s_cls_total[CLS_COUNT];
+    __shared__ unsigned long long s_next;      // this CTA's next work item
+    __shared__ uint32_t s_ncont, s_nregen, s_tile;
+    __shared__ unsigned long long s_clk[3];    // PROF: t_prev, T+S, A
 
-    const uint32_t tid = threadIdx.x, lane = tid & 31, lt_mask = (1u << lane) - 1u;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
     const bool mis = f.strategy == PT_STRATEGY_MIS;
     const uint64_t work_lo = (uint64_t)blockIdx.x * f.chunk, work_hi = work_lo + f.chunk < f.total_work ? work_lo + f.chunk : f.total_work;
 
@@ -120,86 +108,97 @@ __global__ void __launch_bounds__(kSwBlock, 1) k_smem_wavefront(SceneView s, con
     };
     const SceneShared sc{s_prims, s_mats, s_lights, s.n_lights};
 
-    // ---- both halves start with a work list that re-seeds every slot
+    // ---- the first work list re-seeds every slot
     for (uint32_t i = tid; i < (uint32_t)kSwSlots; i += kSwBlock) s_list[i] = (uint16_t)i;
-    if (tid < 3 * sizeof(SwRing) / 4) reinterpret_cast<uint32_t*>(s_ring)[tid] = 0;
-    if (tid < 3) { s_clk[tid] = 0; s_stats[tid] = 0; }
-    uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, phase = 0;   // per-lane counters, reduced once at the end
-    uint64_t base = work_lo;                                         // next unclaimed work item (uniform, tracked by every thread)
-    long long clk_t = 0, clk_a = 0, clk_0 = PROF ? clock64() : 0;
+    if (tid == 0) {
+        s_next = work_lo; s_ncont = 0; s_nregen = kSwSlots; s_tile = 0;
+        if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = 0; }
+    }
+    uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // per-lane counters, reduced once at the end
     __syncthreads();
 
     while (true) {
-        const SwRing& R = s_ring[(phase + 2) % 3];
-        SwRing& W = s_ring[phase % 3];
-        const uint32_t ht = phase & 1, ha = ht ^ 1;                  // halves in the T and A roles
-        // T: entries [0, n_cont) of the work list continue a path; the last n_new take work items base, base+1, ... (entry H-1
-        // first) while the CTA's range lasts.  Slots that find no work drop out of every list for good.
-        const uint32_t n_cont = R.n_cont, n_regen = phase < 2 ? H : R.n_regen;
+        // ---- phase T: entries [0, n_cont) continue a path; the last n_regen entries take new work items base, base+1, ...
+        // from the back (entry kSwSlots-1 first) while the CTA's range lasts.  Entries in between, and re-seed entries past
+        // the end of the range, are dead: they sort last and phase A never touches them.
+        const uint32_t n_cont = s_ncont, n_regen = s_nregen;
+        const uint64_t base = s_next;
         const uint64_t avail = work_hi > base ? work_hi - base : 0;
         const uint32_t n_new = avail < n_regen ? (uint32_t)avail : n_regen;
-        // A: the class lists of the other half
-        const uint32_t n_mir = R.cls[CLS_MIRROR], n_dif = R.cls[CLS_DIFFUSE], n_emi = R.cls[CLS_EMISSIVE], n_mis = R.cls[CLS_MISS];
-        // items of this phase, expensive first: shading tiles (mirror, diffuse), T groups (continuing, re-seed), cheap tiles
-        const uint32_t i0 = (n_mir + 31) / 32, i1 = i0 + (n_dif + 31) / 32, i2 = i1 + (n_cont + 31) / 32, i3 = i2 + (n_new + 31) / 32,
-                       i4 = i3 + (n_emi + 31) / 32, i5 = i4 + (n_mis + 31) / 32;
-        if (i5 == 0) break;                                          // uniform: both halves are empty
-        if (tid < sizeof(SwRing) / 4) reinterpret_cast<uint32_t*>(&s_ring[(phase + 1) % 3])[tid] = 0;
-        uint16_t* list_t = s_list + ht * H; uint16_t* ord_a_t = s_ord_a + ht * H; uint16_t* ord_b_t = s_ord_b + ht * H;
-        uint16_t* list_a = s_list + ha * H; const uint16_t* ord_a_a = s_ord_a + ha * H; const uint16_t* ord_b_a = s_ord_b + ha * H;
-
-        while (true) {
-            uint32_t item = 0;
-            if (lane == 0) item = atomicAdd(&W.item, 1u);
-            item = __shfl_sync(0xffffffffu, item, 0);
-            if (item >= i5) break;
-            const long long t_in = PROF ? clock64() : 0;
-            if (item >= i1 && item < i3) {
-                // ---- T group
-                const bool seed = item >= i2;
-                const uint32_t r = (item - (seed ? i2 : i1)) * 32 + lane;
-                const bool valid = r < (seed ? n_new : n_cont);
-                uint32_t c = CLS_DEAD, j = 0;
-                if (valid) {
-                    j = list_t[seed ? H - 1 - r : r];
-                    float4 ro, rd;
-                    if (seed) {
-                        uint2 m;
-                        make_primary(f, base + r, ro, rd, m);
-                        s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
-                    } else {
-                        ro = s_ro[j]; rd = s_rd[j];
-                    }
-                    float t; int id;
-                    trace_closest(v3(ro), v3(rd), t, id);
-                    s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
-                    if (id < 0) c = CLS_MISS;
-                    else {
-                        uint32_t kind = __float_as_uint(s_mats[2 * id].w);
-                        c = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
-                    }
+        if (n_cont + n_new == 0) break;                              // uniform: nothing left in this CTA
+        if (lane < CLS_COUNT * SPT) s_cls_cnt[lane / SPT][(lane % SPT) * NW + warp] = 0;
+        __syncwarp();
+        uint32_t cls[SPT], rank[SPT], slot[SPT];
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) {
+            const uint32_t e = k * kSwBlock + tid;
+            uint32_t c = CLS_DEAD, j = 0;
+            const bool cont = e < n_cont, seed = e >= kSwSlots - n_new;
+            if (cont || seed) {
+                j = s_list[e];
+                float4 ro, rd;
+                if (seed) {
+                    uint2 m;
+                    make_primary(f, base + (kSwSlots - 1 - e), ro, rd, m);
+                    s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
+                } else {
+                    ro = s_ro[j]; rd = s_rd[j];
                 }
-                // append to the class list: one shared atomic per class present in the warp
-                const uint32_t same = __match_any_sync(0xffffffffu, c);
-                const uint32_t rank = __popc(same & lt_mask);
-                uint32_t pos = 0;
-                if (rank == 0 && valid) pos = atomicAdd(&W.cls[c], (uint32_t)__popc(same));
-                pos = __shfl_sync(0xffffffffu, pos, __ffs(same) - 1) + rank;
-                if (valid) {
-                    uint16_t* ord = (c == CLS_MIRROR || c == CLS_DIFFUSE) ? ord_a_t : ord_b_t;
-                    ord[(c == CLS_MIRROR || c == CLS_EMISSIVE) ? pos : H - 1 - pos] = (uint16_t)j;
+                float t; int id;
+                trace_closest(v3(ro), v3(rd), t, id);
+                s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
+                if (id < 0) c = CLS_MISS;
+                else {
+                    uint32_t kind = __float_as_uint(s_mats[2 * id].w);
+                    c = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
                 }
-                if (PROF) clk_t += clock64() - t_in;
-                continue;
             }
-            // ---- A tile
-            uint32_t idx, cnt; const uint16_t* ord; bool fwd;
-            if (item < i0)      { idx = item * 32 + lane;        cnt = n_mir; ord = ord_a_a; fwd = true; }
-            else if (item < i1) { idx = (item - i0) * 32 + lane; cnt = n_dif; ord = ord_a_a; fwd = false; }
-            else if (item < i4) { idx = (item - i3) * 32 + lane; cnt = n_emi; ord = ord_b_a; fwd = true; }
-            else                { idx = (item - i4) * 32 + lane; cnt = n_mis; ord = ord_b_a; fwd = false; }
-            const bool alive = idx < cnt;
-            const uint32_t j = alive ? ord[fwd ? idx : H - 1 - idx] : ha * H;
+            const uint32_t same = __match_any_sync(0xffffffffu, c);  // lanes of this group in the same class
+            cls[k] = c; slot[k] = j; rank[k] = __popc(same & lt_mask);
+            if (rank[k] == 0) s_cls_cnt[c][k * NW + warp] = (uint16_t)__popc(same);
+        }
+        __syncthreads();
+        if (tid == 0) { s_next = base + n_new; s_ncont = 0; s_nregen = 0; s_tile = 0; }
+        // ---- phase S: counting sort by class.  Warp cc scans the NGRP group counts of class cc (exclusive, in place);
+        // the class bases are the running sum of the five totals.
+        for (uint32_t cc = warp; cc < CLS_COUNT; cc += NW) {
+            uint16_t* row = s_cls_cnt[cc];
+            uint32_t run = 0;
+            for (uint32_t k0 = 0; k0 < NGRP; k0 += 32) {
+                uint32_t k = k0 + lane;
+                uint32_t v = k < NGRP ? row[k] : 0, x = v;
+                for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+                if (k < NGRP) row[k] = (uint16_t)(run + x - v);
+                run += __shfl_sync(0xffffffffu, x, 31);
+            }
+            if (lane == 0) s_cls_total[cc] = run;
+        }
+        __syncthreads();
+        uint32_t n_live;
+        {
+            uint32_t start[CLS_COUNT], acc = 0;
+#pragma unroll
+            for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) { start[cc] = acc; acc += s_cls_total[cc]; }
+            n_live = start[CLS_DEAD];                                // CLS_DEAD is the last class
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) {
+                uint32_t st = 0;
+#pragma unroll
+                for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) st = cls[k] == cc ? start[cc] : st;
+                s_order[st + s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)slot[k];
+            }
+        }
+        __syncthreads();
+        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[1] += t - s_clk[0]; s_clk[0] = t; }
+
+        // ---- phase A: dynamic tiles of the class-sorted list
+        while (true) {
+            uint32_t tile = 0;
+            if (lane == 0) tile = atomicAdd(&s_tile, 1u);
+            tile = __shfl_sync(0xffffffffu, tile, 0);
+            if (tile * 32 >= n_live) break;
+            const bool alive = tile * 32 + lane < n_live;
+            const uint32_t j = alive ? s_order[tile * 32 + lane] : 0u;
             const uint2 meta = s_meta[j];
             bool finished = false, emit_shadow = false;
             float3 sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f), p_hit = v3(0.f, 0.f, 0.f);
@@ -225,49 +224,43 @@ __global__ void __launch_bounds__(kSwBlock, 1) k_smem_wavefront(SceneView s, con
                 ++c_shadow;
                 if (!trace_any(p_hit, sh_d, sh_tmax)) atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
             }
-            // next work list of this half: continuing slots from the front, slots to re-seed from the back
+            // next work list: continuing slots from the front, slots to re-seed from the back
             {
                 const uint32_t fin = __ballot_sync(0xffffffffu, alive && finished), con = __ballot_sync(0xffffffffu, alive && !finished);
                 uint32_t b = 0;
-                if (lane == 0 && fin) b = atomicAdd(&W.n_regen, (uint32_t)__popc(fin));
-                if (lane == 1 && con) b = atomicAdd(&W.n_cont, (uint32_t)__popc(con));
+                if (lane == 0 && fin) b = atomicAdd(&s_nregen, (uint32_t)__popc(fin));
+                if (lane == 1 && con) b = atomicAdd(&s_ncont, (uint32_t)__popc(con));
                 const uint32_t bfin = __shfl_sync(0xffffffffu, b, 0), bcon = __shfl_sync(0xffffffffu, b, 1);
-                if (alive) list_a[finished ? H - 1 - (bfin + __popc(fin & lt_mask)) : bcon + __popc(con & lt_mask)] = (uint16_t)j;
+                if (alive) s_list[finished ? kSwSlots - 1 - (bfin + __popc(fin & lt_mask)) : bcon + __popc(con & lt_mask)] = (uint16_t)j;
             }
-            if (PROF) clk_a += clock64() - t_in;
         }
-        base += n_new;
-        ++phase;
+        ++iters;
         __syncthreads();
+        if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
     }
 
     // ---- bookkeeping
+    __shared__ uint32_t s_stats[3];
+    if (tid < 3) s_stats[tid] = 0;
+    __syncthreads();
     c_shadow = __reduce_add_sync(0xffffffffu, c_shadow); c_scatter = __reduce_add_sync(0xffffffffu, c_scatter); c_vertex = __reduce_add_sync(0xffffffffu, c_vertex);
-    if (lane == 0) {
-        atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex);
-        if (PROF) {
-            atomicAdd(&s_clk[0], (unsigned long long)clk_t); atomicAdd(&s_clk[1], (unsigned long long)clk_a);
-            atomicAdd(&s_clk[2], (unsigned long long)(clock64() - clk_0));
-        }
-    }
+    if (lane == 0) { atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex); }
     __syncthreads();
     if (tid == 0) {
-        out.block_stats[blockIdx.x] = make_uint4((uint32_t)(base - work_lo), s_stats[0], s_stats[1], s_stats[2]);
-        out.block_iters[blockIdx.x] = phase;
-        if (PROF) {
-            out.block_clk[3 * blockIdx.x] = s_clk[0]; out.block_clk[3 * blockIdx.x + 1] = s_clk[1];
-            out.block_clk[3 * blockIdx.x + 2] = s_clk[2] - s_clk[0] - s_clk[1];
-        }
+        out.block_stats[blockIdx.x] = make_uint4((uint32_t)(s_next - work_lo), s_stats[0], s_stats[1], s_stats[2]);
+        out.block_iters[blockIdx.x] = iters;
+        if (PROF) { out.block_clk[3 * blockIdx.x] = s_clk[1]; out.block_clk[3 * blockIdx.x + 1] = s_clk[2]; out.block_clk[3 * blockIdx.x + 2] = 0; }
     }
 }
 
 }  // namespace
 
-// Whether the shared-memory wavefront applies to this scene: the slot state plus the staged scene must fit one SM.
+// Whether the shared-memory wavefront applies to this scene: the queues plus the staged scene must leave room for at
+// least three CTAs per SM (occupancy is what hides the barriers between phases).
 bool smem_wavefront_applicable(const pt_context* ctx, const SceneDev& scene, bool brute) {
     (void)ctx;
     size_t bytes = sw_smem_bytes(scene.n_objects, scene.n_nodes, scene.n_lights, brute) + 1024;
-    return scene.n_objects > 0 && scene.n_objects <= kMaxSmemPrims && bytes <= 227 * 1024;
+    return scene.n_objects > 0 && scene.n_objects <= kMaxSmemPrims && bytes * (kSwMinBlocks < 3 ? kSwMinBlocks : 3) <= 227 * 1024;
 }
 
 int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, pt_stats* stats) {
