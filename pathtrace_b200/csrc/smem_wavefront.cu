@@ -53,7 +53,7 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
     b += 8 * (size_t)kSwSlots * 2;                  // hit, meta
     b += 16 * ((brute ? 0 : (size_t)n_nodes * 4) + (size_t)n_objects * 4 + (size_t)n_objects * 2);
     b += 4 * (((size_t)n_lights + 3) & ~size_t(3));
-    b += 2 * 2 * (((size_t)kSwSlots + 7) & ~size_t(7));   // sorted order, next work list
+    b += 2 * 3 * (((size_t)kSwSlots + 7) & ~size_t(7));   // two class-list arrays, next work list
     b += brute ? 16 * 5 * (size_t)n_objects : 0;    // brute-force scan table (at most one entry per object)
     return b;
 }
@@ -75,13 +75,16 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     float4* s_prims = s_nodes + (BRUTE ? 0 : s.n_nodes * 4);
     float4* s_mats = s_prims + s.n_objects * 4;
     uint32_t* s_lights = reinterpret_cast<uint32_t*>(s_mats + s.n_objects * 2);
-    uint16_t* s_order = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));   // class-sorted slots (phase A reads)
-    uint16_t* s_list = s_order + ((kSwSlots + 7) & ~7);                                     // next work list (phase A writes)
-    float4* s_brute = reinterpret_cast<float4*>(s_list + ((kSwSlots + 7) & ~7));
-    __shared__ uint16_t s_cls_cnt[CLS_COUNT][NGRP];
-    __shared__ uint32_t s_cls_total[CLS_COUNT];
-    __shared__ unsigned long long s_next;      // this CTA's next work item
-    __shared__ uint32_t s_ncont, s_nregen, s_tile;
+    constexpr uint32_t LST = (kSwSlots + 7) & ~7;
+    uint16_t* s_ord_a = reinterpret_cast<uint16_t*>(s_lights + ((s.n_lights + 3) & ~3u));   // class lists: mirror ->  <- diffuse
+    uint16_t* s_ord_b = s_ord_a + LST;                                                      //              emissive ->  <- miss
+    uint16_t* s_list = s_ord_b + LST;                                                       // next work list (phase A writes)
+    float4* s_brute = reinterpret_cast<float4*>(s_list + LST);
+    // Counters alternate between two copies so that none is reset while a straggler may still read it: iteration i counts the
+    // classes in s_cls[i & 1] and reads its work list sizes from s_len[i & 1]; phase A of iteration i fills s_len[(i + 1) & 1].
+    __shared__ uint32_t s_cls[2][4];           // entries per class list
+    __shared__ uint32_t s_len[2][2];           // next work list: continuing entries (front), entries to re-seed (back)
+    __shared__ uint32_t s_tile;
     __shared__ unsigned long long s_clk[3];    // PROF: t_prev, T+S, A
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
@@ -111,24 +114,24 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     // ---- the first work list re-seeds every slot
     for (uint32_t i = tid; i < (uint32_t)kSwSlots; i += kSwBlock) s_list[i] = (uint16_t)i;
     if (tid == 0) {
-        s_next = work_lo; s_ncont = 0; s_nregen = kSwSlots; s_tile = 0;
+        s_len[0][0] = 0; s_len[0][1] = kSwSlots; s_tile = 0;
+        for (int c = 0; c < 4; ++c) s_cls[0][c] = s_cls[1][c] = 0;
         if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = 0; }
     }
     uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // per-lane counters, reduced once at the end
+    uint64_t base = work_lo;                                         // next unclaimed work item (uniform, tracked by every thread)
     __syncthreads();
 
     while (true) {
         // ---- phase T: entries [0, n_cont) continue a path; the last n_regen entries take new work items base, base+1, ...
         // from the back (entry kSwSlots-1 first) while the CTA's range lasts.  Entries in between, and re-seed entries past
         // the end of the range, are dead: they sort last and phase A never touches them.
-        const uint32_t n_cont = s_ncont, n_regen = s_nregen;
-        const uint64_t base = s_next;
+        const uint32_t par = iters & 1;
+        const uint32_t n_cont = s_len[par][0], n_regen = s_len[par][1];
         const uint64_t avail = work_hi > base ? work_hi - base : 0;
         const uint32_t n_new = avail < n_regen ? (uint32_t)avail : n_regen;
         if (n_cont + n_new == 0) break;                              // uniform: nothing left in this CTA
-        if (lane < CLS_COUNT * SPT) s_cls_cnt[lane / SPT][(lane % SPT) * NW + warp] = 0;
-        __syncwarp();
-        uint32_t cls[SPT], rank[SPT], slot[SPT];
+        if (tid == 0) { s_len[par ^ 1][0] = 0; s_len[par ^ 1][1] = 0; s_tile = 0; }
 #pragma unroll
         for (int k = 0; k < SPT; ++k) {
             const uint32_t e = k * kSwBlock + tid;
@@ -153,52 +156,36 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                     c = kind == PT_MATK_MIRROR ? CLS_MIRROR : kind == PT_MATK_EMISSIVE ? CLS_EMISSIVE : CLS_DIFFUSE;
                 }
             }
-            const uint32_t same = __match_any_sync(0xffffffffu, c);  // lanes of this group in the same class
-            cls[k] = c; slot[k] = j; rank[k] = __popc(same & lt_mask);
-            if (rank[k] == 0) s_cls_cnt[c][k * NW + warp] = (uint16_t)__popc(same);
-        }
-        __syncthreads();
-        if (tid == 0) { s_next = base + n_new; s_ncont = 0; s_nregen = 0; s_tile = 0; }
-        // ---- phase S: counting sort by class.  Warp cc scans the NGRP group counts of class cc (exclusive, in place);
-        // the class bases are the running sum of the five totals.
-        for (uint32_t cc = warp; cc < CLS_COUNT; cc += NW) {
-            uint16_t* row = s_cls_cnt[cc];
-            uint32_t run = 0;
-            for (uint32_t k0 = 0; k0 < NGRP; k0 += 32) {
-                uint32_t k = k0 + lane;
-                uint32_t v = k < NGRP ? row[k] : 0, x = v;
-                for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-                if (k < NGRP) row[k] = (uint16_t)(run + x - v);
-                run += __shfl_sync(0xffffffffu, x, 31);
-            }
-            if (lane == 0) s_cls_total[cc] = run;
-        }
-        __syncthreads();
-        uint32_t n_live;
-        {
-            uint32_t start[CLS_COUNT], acc = 0;
-#pragma unroll
-            for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) { start[cc] = acc; acc += s_cls_total[cc]; }
-            n_live = start[CLS_DEAD];                                // CLS_DEAD is the last class
-#pragma unroll
-            for (int k = 0; k < SPT; ++k) {
-                uint32_t st = 0;
-#pragma unroll
-                for (uint32_t cc = 0; cc < CLS_COUNT; ++cc) st = cls[k] == cc ? start[cc] : st;
-                s_order[st + s_cls_cnt[cls[k]][k * NW + warp] + rank[k]] = (uint16_t)slot[k];
+            // append to the class list: one shared atomic per class present in the warp
+            const uint32_t same = __match_any_sync(0xffffffffu, c);
+            const uint32_t rank = __popc(same & lt_mask);
+            uint32_t pos = 0;
+            if (rank == 0 && c != CLS_DEAD) pos = atomicAdd(&s_cls[par][c], (uint32_t)__popc(same));
+            pos = __shfl_sync(0xffffffffu, pos, __ffs(same) - 1) + rank;
+            if (c != CLS_DEAD) {
+                uint16_t* ord = (c == CLS_MIRROR || c == CLS_DIFFUSE) ? s_ord_a : s_ord_b;
+                ord[(c == CLS_MIRROR || c == CLS_EMISSIVE) ? pos : kSwSlots - 1 - pos] = (uint16_t)j;
             }
         }
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[1] += t - s_clk[0]; s_clk[0] = t; }
+        if (tid < 4) s_cls[par ^ 1][tid] = 0;
+        const uint32_t n_mir = s_cls[par][CLS_MIRROR], n_dif = s_cls[par][CLS_DIFFUSE], n_emi = s_cls[par][CLS_EMISSIVE], n_mis = s_cls[par][CLS_MISS];
+        const uint32_t i0 = (n_mir + 31) / 32, i1 = i0 + (n_dif + 31) / 32, i2 = i1 + (n_emi + 31) / 32, i3 = i2 + (n_mis + 31) / 32;
 
         // ---- phase A: dynamic tiles of the class-sorted list
         while (true) {
             uint32_t tile = 0;
             if (lane == 0) tile = atomicAdd(&s_tile, 1u);
             tile = __shfl_sync(0xffffffffu, tile, 0);
-            if (tile * 32 >= n_live) break;
-            const bool alive = tile * 32 + lane < n_live;
-            const uint32_t j = alive ? s_order[tile * 32 + lane] : 0u;
+            if (tile >= i3) break;
+            uint32_t idx, cnt; const uint16_t* ord; bool fwd;         // expensive tiles first: mirror, diffuse, emissive, miss
+            if (tile < i0)      { idx = tile * 32 + lane;        cnt = n_mir; ord = s_ord_a; fwd = true; }
+            else if (tile < i1) { idx = (tile - i0) * 32 + lane; cnt = n_dif; ord = s_ord_a; fwd = false; }
+            else if (tile < i2) { idx = (tile - i1) * 32 + lane; cnt = n_emi; ord = s_ord_b; fwd = true; }
+            else                { idx = (tile - i2) * 32 + lane; cnt = n_mis; ord = s_ord_b; fwd = false; }
+            const bool alive = idx < cnt;
+            const uint32_t j = alive ? ord[fwd ? idx : kSwSlots - 1 - idx] : 0u;
             const uint2 meta = s_meta[j];
             bool finished = false, emit_shadow = false;
             float3 sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f), p_hit = v3(0.f, 0.f, 0.f);
@@ -228,13 +215,14 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             {
                 const uint32_t fin = __ballot_sync(0xffffffffu, alive && finished), con = __ballot_sync(0xffffffffu, alive && !finished);
                 uint32_t b = 0;
-                if (lane == 0 && fin) b = atomicAdd(&s_nregen, (uint32_t)__popc(fin));
-                if (lane == 1 && con) b = atomicAdd(&s_ncont, (uint32_t)__popc(con));
+                if (lane == 0 && fin) b = atomicAdd(&s_len[par ^ 1][1], (uint32_t)__popc(fin));
+                if (lane == 1 && con) b = atomicAdd(&s_len[par ^ 1][0], (uint32_t)__popc(con));
                 const uint32_t bfin = __shfl_sync(0xffffffffu, b, 0), bcon = __shfl_sync(0xffffffffu, b, 1);
                 if (alive) s_list[finished ? kSwSlots - 1 - (bfin + __popc(fin & lt_mask)) : bcon + __popc(con & lt_mask)] = (uint16_t)j;
             }
         }
         ++iters;
+        base += n_new;
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
     }
@@ -247,7 +235,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     if (lane == 0) { atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex); }
     __syncthreads();
     if (tid == 0) {
-        out.block_stats[blockIdx.x] = make_uint4((uint32_t)(s_next - work_lo), s_stats[0], s_stats[1], s_stats[2]);
+        out.block_stats[blockIdx.x] = make_uint4((uint32_t)(base - work_lo), s_stats[0], s_stats[1], s_stats[2]);
         out.block_iters[blockIdx.x] = iters;
         if (PROF) { out.block_clk[3 * blockIdx.x] = s_clk[1]; out.block_clk[3 * blockIdx.x + 1] = s_clk[2]; out.block_clk[3 * blockIdx.x + 2] = 0; }
     }
