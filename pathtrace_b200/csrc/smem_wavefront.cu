@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         const uint32_t n_new = avail < n_regen ? (uint32_t)avail : n_regen;
         if (n_cont + n_new == 0) break;                              // uniform: nothing left in this CTA
         if (tid == 0) { s_len[par ^ 1][0] = 0; s_len[par ^ 1][1] = 0; s_tile = 0; }
-#pragma unroll
+#pragma unroll 1                                                     // one copy of the scan: the instruction cache is 32 KB
         for (int k = 0; k < SPT; ++k) {
             const uint32_t e = k * kSwBlock + tid;
             uint32_t c = CLS_DEAD, j = 0;
