@@ -16,6 +16,8 @@
 #include <cstdio>
 #include <vector>
 
+#include <cstdlib>
+
 #include "pt_wave.cuh"
 
 using namespace ptw;
@@ -111,6 +113,67 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
         float4 c = pool.sh_c[i];                       // K8: color_temp += ..., world.rs:296-313
         atomicAdd(accum + __float_as_uint(d.w), make_float4(c.x, c.y, c.z, 0.f));
     }
+}
+
+// K3 / K5 for scenes that walk the LBVH (pt_wave.cuh: bvh_stream).  A resident grid of warps; warp w owns the slots
+// [w * per_warp, (w + 1) * per_warp) of the queue and streams them through its lanes.
+// Occupancy: walking the LBVH through L2 (C4) is bound by memory latency and gains from every extra warp (8 CTAs = 32
+// registers per thread, spills included: 290 -> 314 Msamples/s); walking it in shared memory (C3) is compute-bound and loses
+// (934 -> 765), so that one keeps its registers.
+template <bool SMEM>
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : 8) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t per_warp) {
+    extern __shared__ float4 smem[];
+    Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    uint32_t cursor = (blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * per_warp;
+    const uint32_t end = cursor + per_warp < pool.P ? cursor + per_warp : pool.P;
+    auto next = [&](bool want, uint32_t idle, float3& o, float3& d, float& tm, uint32_t& slot, bool& exhausted) {
+        bool got = false;
+        const uint32_t i = cursor + __popc(idle & lt);
+        if (want && i < end && (pool.meta[i].x >> 31) != 0u) {
+            o = v3(pool.ray_o[i]); d = v3(pool.ray_d[i]); tm = __int_as_float(0x7f800000); slot = i; got = true;
+        }
+        cursor += __popc(idle);
+        exhausted = cursor >= end;
+        return got;
+    };
+    auto finish = [&](uint32_t slot, float t, int id) { pool.hit[slot] = make_uint2(__float_as_uint(t), (uint32_t)id); };
+    if (cursor < end) bvh_stream<SMEM, false>(g, t_min, next, finish);
+}
+template <bool SMEM>
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : 8) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t per_warp) {
+    extern __shared__ float4 smem[];
+    Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
+    const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    uint32_t cursor = (blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * per_warp;
+    const uint32_t end = cursor + per_warp < pool.P ? cursor + per_warp : pool.P;
+    // the shadow queue is dense per shade-CTA segment: entries [seg * kShadeSlots, seg * kShadeSlots + seg_count[seg])
+    auto next = [&](bool want, uint32_t idle, float3& o, float3& d, float& tm, uint32_t& slot, bool& exhausted) {
+        uint32_t take = 0;
+        while (cursor < end) {                                       // warp-uniform: skip the empty tail of a segment
+            const uint32_t seg = cursor / kShadeSlots, off = cursor % kShadeSlots, cnt = pool.seg_count[seg];
+            if (off >= cnt) { cursor = (seg + 1) * kShadeSlots; continue; }
+            take = min(min((uint32_t)__popc(idle), cnt - off), end - cursor);
+            break;
+        }
+        bool got = false;
+        const uint32_t r = __popc(idle & lt);
+        if (want && r < take) {
+            const uint32_t i = cursor + r;
+            const float4 so = pool.sh_o[i], sd = pool.sh_d[i];
+            o = v3(so); d = v3(sd); tm = so.w; slot = i; got = true;
+        }
+        cursor += take;
+        exhausted = cursor >= end;
+        return got;
+    };
+    auto finish = [&](uint32_t slot, float, int id) {
+        if (id < 0) {                                                // unoccluded: K8, color_temp += ..., world.rs:296-313
+            const float4 c = pool.sh_c[slot];
+            atomicAdd(accum + __float_as_uint(pool.sh_d[slot].w), make_float4(c.x, c.y, c.z, 0.f));
+        }
+    };
+    if (cursor < end) bvh_stream<SMEM, true>(g, t_min, next, finish);
 }
 
 // ------------------------------------------------------------------------------------ shade
@@ -487,6 +550,28 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #define SETS(S, B) { rc = set_smem(ctx, k_trace_closest<S, B>, mode.smem_bytes); if (rc) return rc; rc = set_smem(ctx, k_trace_shadow<S, B>, mode.smem_bytes); if (rc) return rc; }
     PT_DISPATCH(mode, SETS);
 #undef SETS
+    // LBVH scenes: a resident grid of warps streams the queues (k_trace_*_stream); env PT_NO_STREAM_BVH=1 keeps one thread
+    // per slot (A/B runs)
+    static const bool no_stream = getenv("PT_NO_STREAM_BVH") != nullptr;
+    const bool stream_bvh = !mode.brute && scene.n_objects >= 2 && !no_stream;
+    uint32_t stream_grid = 0, per_warp = 0;
+    if (stream_bvh) {
+        int occ_c = 0, occ_s = 0;
+        if (mode.smem) {
+            rc = set_smem(ctx, k_trace_closest_stream<true>, mode.smem_bytes); if (rc) return rc;
+            rc = set_smem(ctx, k_trace_shadow_stream<true>, mode.smem_bytes); if (rc) return rc;
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_trace_closest_stream<true>, kBlock, mode.smem_bytes));
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, k_trace_shadow_stream<true>, kBlock, mode.smem_bytes));
+        } else {
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_trace_closest_stream<false>, kBlock, 0));
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, k_trace_shadow_stream<false>, kBlock, 0));
+        }
+        const int occ = occ_c < occ_s ? occ_c : occ_s;
+        if (occ < 1) { ctx->err = "stream traversal kernels do not fit on an SM"; return PT_ERR_CUDA; }
+        stream_grid = (uint32_t)ctx->sm_count * (uint32_t)occ * 2u;   // two waves: a long walk at the end of a range costs half as much
+        const uint32_t n_warps = stream_grid * (kBlock / 32);
+        per_warp = ((P + n_warps - 1) / n_warps + 31) / 32 * 32;
+    }
     const uint32_t sgrid = P / kShadeSlots;
     f.chunk = (f.total_work + sgrid - 1) / sgrid;
     const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
@@ -516,7 +601,10 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         for (int it = 0; it < kItersPerBatch; ++it) {
 #define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
             prof_begin(PT_K_TRACE_CLOSEST);
-            PT_DISPATCH(mode, TRACE);
+            if (stream_bvh) {
+                if (mode.smem) k_trace_closest_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, per_warp);
+                else k_trace_closest_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, per_warp);
+            } else PT_DISPATCH(mode, TRACE);
             prof_end();
 #undef TRACE
             prof_begin(PT_K_SHADE);
@@ -526,7 +614,10 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
             if (mis) {
                 prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
-                PT_DISPATCH(mode, SHADOW);
+                if (stream_bvh) {
+                    if (mode.smem) k_trace_shadow_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, per_warp);
+                    else k_trace_shadow_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, per_warp);
+                } else PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
                 prof_end();
                 launches++;
