@@ -69,6 +69,25 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+HOST_DIR = os.path.join(os.path.dirname(_HERE), "host")
+HOST_BIN = os.path.join(LIBDIR, "pathtrace_host")
+
+
+def build_host(force: bool = False) -> str:
+    """The compiled-language host side above the C ABI (host/pathtrace_host.hpp: the reference's World / Object / Camera API in
+    C++17) and its headless `main` (host/main.cpp, the stand-in for src/main.rs), linked against the in-tree library."""
+    lib = build_library()
+    srcs = [os.path.join(HOST_DIR, "main.cpp"), os.path.join(HOST_DIR, "pathtrace_host.hpp"), os.path.join(_HERE, "..", "include", "pathtrace_b200.h")]
+    if not force and os.path.exists(HOST_BIN) and all(os.path.getmtime(HOST_BIN) >= os.path.getmtime(d) for d in srcs + [lib]):
+        return HOST_BIN
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", srcs[0], "-o", HOST_BIN, "-L" + LIBDIR, "-lpathtrace_b200", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode:
+        raise RuntimeError(f"host build failed:\n{r.stdout}\n{r.stderr}")
+    return HOST_BIN
+
+
 if __name__ == "__main__":
     import sys
     print(build_library(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

@@ -127,6 +127,10 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
             if (std::sqrt((double)e[0] * e[0] + (double)e[1] * e[1] + (double)e[2] * e[2]) > 0.0) lights.push_back(i);
         }
     sc->dev.n_lights = (uint32_t)lights.size();
+    sc->dev.fp32_domain = true;
+    for (uint32_t i = 0; i < n && sc->dev.fp32_domain; ++i)
+        for (int k = 0; k < (shapes[i].kind == PT_SHAPE_TRIANGLE ? 9 : 4); ++k)
+            if (!(std::fabs(shapes[i].v[k]) <= kFp32DomainMax)) { sc->dev.fp32_domain = false; break; }
     if (n && n <= 1024) {   // brute-force scan table: consecutive triangles share an entry (lbvh.cu: k_brute_table walks the same way)
         uint32_t e = 0, pairs = 0;
         for (uint32_t i = 0; i < n; ++e) {

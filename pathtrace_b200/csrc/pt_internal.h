@@ -8,6 +8,7 @@
 
 #include "../../include/pathtrace_b200.h"
 
+constexpr float kFp32DomainMax = 4294967296.0f;   // 2^32, see SceneDev::fp32_domain
 constexpr int kBruteParamPairs = 8;   // pair entries of the scan table that can travel as a kernel parameter (pt_wave.cuh: BruteParam)
 
 // Scene resident in HBM (replicated per GPU).  All arrays are float4-packed for 128-bit loads.
@@ -19,6 +20,10 @@ struct SceneDev {
     float4* nodes = nullptr;      // 4 x float4 per LBVH node (64 B): [Llo,left][Lhi,right][Rlo,0][Rhi,0]
     float4* brute = nullptr;      // brute-force scan table, 5 x float4 per entry (see k_brute_table); scenes <= 1024 objects only
     uint32_t n_brute = 0, n_pairs = 0;   // entries; the first n_pairs are triangle pairs
+    // Every shape coordinate (vertices, centres, radii) is finite with magnitude <= kFp32DomainMax: no intermediate of the
+    // triangle test can overflow, and every determinant is either below the 1e-8 rejection threshold or a normal number far
+    // from 2^126 — the precondition of the unchecked pair test (pt_math.cuh: prcp_rn<false>, hit_triangle2<false, .>).
+    bool fp32_domain = false;
     std::vector<float4> brute_host;      // host copy of the pair entries that fit a kernel parameter (pt_wave.cuh: BruteParam)
     uint32_t* codes_sorted = nullptr;
     uint32_t* prim_sorted = nullptr;

@@ -98,58 +98,63 @@ PT_DEV bool slab(float3 lo, float3 hi, float3 ro, float3 inv, float t_min, float
 // Both tests of a pair see the t_max in force before the pair and the updates re-check the inclusive bound in index order, so
 // the pairs alone reproduce the sequential scan of world.rs:281-287 (ties go to the later object).  The unpaired primitives
 // come after every pair, out of index order, and therefore break ties on the object index explicitly.
+template <bool CHECKED = true>
 PT_DEV void pair_closest(float4 A, float4 B, float4 C, float4 D, float4 E, float3 ro, float3 rd, float t_min, float& tmax, int& best_id) {
     bool oka, okb;
-    float2 t = hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
-                             pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax, oka, okb);
+    float2 t = hit_triangle2<CHECKED, false>(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y),
+                                             pk(D.z, D.w), pk(E.x, E.y), ro, rd, t_min, tmax, oka, okb);
     if (oka) { tmax = t.x; best_id = __float_as_int(E.z); }
-    if (okb & (t.y <= tmax)) { tmax = t.y; best_id = __float_as_int(E.w); }
+    if (okb & (t.y <= tmax)) { tmax = t.y; best_id = __float_as_int(E.w); }   // also lane b's upper test: tmax <= the bound before the pair
 }
 PT_DEV void single_closest(float4 q0, float4 q1, float4 q2, float4 E, float3 ro, float3 rd, float t_min, float& tmax, int& best_id) {
     const int id = __float_as_int(E.z);
     float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
     if (t >= 0.0f && (t < tmax || id > best_id)) { tmax = t; best_id = id; }
 }
+template <bool CHECKED = true>
 PT_DEV bool pair_any(float4 A, float4 B, float4 C, float4 D, float4 E, float3 ro, float3 rd, float t_min, float t_max) {
     bool oka, okb;
-    hit_triangle2(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y), pk(D.z, D.w),
-                  pk(E.x, E.y), ro, rd, t_min, t_max, oka, okb);
+    hit_triangle2<CHECKED, true>(pk(A.x, A.y), pk(A.z, A.w), pk(B.x, B.y), pk(B.z, B.w), pk(C.x, C.y), pk(C.z, C.w), pk(D.x, D.y), pk(D.z, D.w),
+                                 pk(E.x, E.y), ro, rd, t_min, t_max, oka, okb);
     return oka | okb;
 }
-// The first kParamPairs pairs of the table can also travel as a kernel parameter: the scan then takes its triangle operands
+// Up to kParamPairs pairs of the table can also travel as a kernel parameter: the scan then takes its triangle operands
 // from the constant bank through uniform registers (no shared-memory loads, no vector registers) — the small-scene form the
-// shared-memory wavefront uses.  The loops stay rolled: the instruction cache is 32 KB and every warp of the CTA runs them.
+// shared-memory wavefront uses (only when ALL pairs fit).  The pairs are RIGHT-aligned in the parameter (pair j of n sits in
+// slot kParamPairs - n + j), so the unrolled scan is entered once, at the slot of the first pair, and runs to the end in
+// ascending object order without a per-pair exit test.
 constexpr int kParamPairs = kBruteParamPairs;
+static_assert(kParamPairs == 8, "the unrolled scans below are written for 8 slots");
 struct BruteParam { float4 e[5 * kParamPairs]; };
-template <class G>
+#define PT_PARAM_SCAN(n_pairs, STEP)                                                                                          \
+    switch (n_pairs) {                                                                                                        \
+        case 8: STEP(0) [[fallthrough]];                                                                                      \
+        case 7: STEP(1) [[fallthrough]];                                                                                      \
+        case 6: STEP(2) [[fallthrough]];                                                                                      \
+        case 5: STEP(3) [[fallthrough]];                                                                                      \
+        case 4: STEP(4) [[fallthrough]];                                                                                      \
+        case 3: STEP(5) [[fallthrough]];                                                                                      \
+        case 2: STEP(6) [[fallthrough]];                                                                                      \
+        case 1: STEP(7) [[fallthrough]];                                                                                      \
+        default: break;                                                                                                       \
+    }
+template <bool CHECKED, class G>
 PT_DEV void closest_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
     best_t = FLT_MAX; best_id = -1;
     float tmax = __int_as_float(0x7f800000);
-#if PT_ROLL_CLOSEST
-#pragma unroll 1
-#else
-#pragma unroll
-#endif
-    for (int e = 0; e < kParamPairs; ++e) {
-        if (e >= (int)g.n_pairs) break;
-        pair_closest(bp.e[5 * e], bp.e[5 * e + 1], bp.e[5 * e + 2], bp.e[5 * e + 3], bp.e[5 * e + 4], ro, rd, t_min, tmax, best_id);
-    }
+#define PT_STEP(k) pair_closest<CHECKED>(bp.e[5 * (k)], bp.e[5 * (k) + 1], bp.e[5 * (k) + 2], bp.e[5 * (k) + 3], bp.e[5 * (k) + 4], ro, rd, t_min, tmax, best_id);
+    PT_PARAM_SCAN(g.n_pairs, PT_STEP)
+#undef PT_STEP
     for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
         single_closest(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 4], ro, rd, t_min, tmax, best_id);
     if (best_id >= 0) best_t = tmax;
 }
-template <class G>
+template <bool CHECKED, class G>
 PT_DEV bool any_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd, float t_min, float t_max) {
     bool occluded = false;
-#if PT_ROLL_ANY
-#pragma unroll 1
-#else
-#pragma unroll
-#endif
-    for (int e = 0; e < kParamPairs; ++e) {
-        if (e >= (int)g.n_pairs) break;
-        occluded |= pair_any(bp.e[5 * e], bp.e[5 * e + 1], bp.e[5 * e + 2], bp.e[5 * e + 3], bp.e[5 * e + 4], ro, rd, t_min, t_max);
-    }
+#define PT_STEP(k) occluded |= pair_any<CHECKED>(bp.e[5 * (k)], bp.e[5 * (k) + 1], bp.e[5 * (k) + 2], bp.e[5 * (k) + 3], bp.e[5 * (k) + 4], ro, rd, t_min, t_max);
+    PT_PARAM_SCAN(g.n_pairs, PT_STEP)
+#undef PT_STEP
     for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
         occluded |= hit_prim(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], ro, rd, t_min, t_max) >= 0.0f;
     return occluded;

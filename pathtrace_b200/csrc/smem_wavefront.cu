@@ -25,6 +25,7 @@
 //
 // HBM traffic is what the algorithm needs: one float4 atomic add per finished path / unoccluded shadow ray.
 // CTAs never communicate, so one launch renders the frame: no per-bounce launches, no host round trips.
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -77,7 +78,8 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
 }
 
 // MODE 0: LBVH from shared memory; 1: scan table from shared memory; 2: its triangle pairs from the kernel parameter `bp`
-// (constant bank, unrolled) and only the unpaired primitives from shared memory.
+// (constant bank, unrolled) and only the unpaired primitives from shared memory; 3: as 2 for scenes and cameras inside the
+// FP32 coordinate domain (SceneDev::fp32_domain): the pair test without the reciprocal's range check and without `u <= 1`.
 template <int MODE, bool PROF>
 __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
                                                                            const __grid_constant__ BruteParam bp) {
@@ -120,11 +122,11 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         g.brute = s_brute; g.n_brute = s.n_brute; g.n_pairs = s.n_pairs;
     }
     auto trace_closest = [&](float3 ro, float3 rd, float& t, int& id) {
-        if (MODE == 2) closest_hit_param(bp, g, ro, rd, f.t_min, t, id);
+        if (MODE >= 2) closest_hit_param<MODE == 2>(bp, g, ro, rd, f.t_min, t, id);
         else closest_hit<true, BRUTE>(g, s.n_objects, ro, rd, f.t_min, t, id);
     };
     auto trace_any = [&](float3 ro, float3 rd, float t_max) -> bool {
-        if (MODE == 2) return any_hit_param(bp, g, ro, rd, f.t_min, t_max);
+        if (MODE >= 2) return any_hit_param<MODE == 2>(bp, g, ro, rd, f.t_min, t_max);
         return any_hit<true, BRUTE>(g, s.n_objects, ro, rd, f.t_min, t_max);
     };
     const SceneShared sc{s_prims, s_mats, s_lights, s.n_lights};
@@ -285,10 +287,14 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
     };
     // brute force over a table whose pairs all fit the kernel parameter: MODE 2 (env PT_SW_NO_PARAM=1 keeps MODE 1, for A/B runs)
     static const bool no_param = getenv("PT_SW_NO_PARAM") != nullptr;
-    const int mode = !brute ? 0 : (scene.brute && scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty() && !no_param) ? 2 : 1;
+    static const bool checked = getenv("PT_SW_CHECKED") != nullptr;   // A/B runs: keep MODE 2 where MODE 3 applies
+    auto in_domain = [](const float* v) { for (int k = 0; k < 3; ++k) if (!(fabsf(v[k]) <= kFp32DomainMax)) return false; return true; };
+    const bool unchecked = scene.fp32_domain && in_domain(rl.cam.origin) && !checked;
+    const int mode = !brute ? 0 : (scene.brute && scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty() && !no_param) ? (unchecked ? 3 : 2) : 1;
     BruteParam bp;
     memset(&bp, 0, sizeof(bp));
-    if (mode == 2) memcpy(bp.e, scene.brute_host.data(), sizeof(float4) * scene.brute_host.size());
+    if (mode >= 2)   // right-aligned: the scan is entered at slot kParamPairs - n_pairs (pt_wave.cuh: PT_PARAM_SCAN)
+        memcpy(bp.e + 5 * ((size_t)kParamPairs - scene.n_pairs), scene.brute_host.data(), sizeof(float4) * 5 * (size_t)scene.n_pairs);
     int occ = 0, rc;
     auto with_kernel = [&](auto&& fn) -> int {
         switch (mode * 2 + (profile ? 1 : 0)) {
@@ -297,7 +303,9 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
             case 2: return fn(k_smem_wavefront<1, false>);
             case 3: return fn(k_smem_wavefront<1, true>);
             case 4: return fn(k_smem_wavefront<2, false>);
-            default: return fn(k_smem_wavefront<2, true>);
+            case 5: return fn(k_smem_wavefront<2, true>);
+            case 6: return fn(k_smem_wavefront<3, false>);
+            default: return fn(k_smem_wavefront<3, true>);
         }
     };
     rc = with_kernel([&](auto kernel) { return pick(kernel, occ); });
