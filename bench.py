@@ -21,7 +21,16 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly one JSON line: file descriptor 1 is pointed at stderr for the whole run (NCCL prints its version
+# banner with the C runtime, past sys.stdout and past NCCL_DEBUG_FILE) and the line is written to the saved descriptor.
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict):
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
+
 
 import numpy as np  # noqa: E402
 
@@ -132,7 +141,7 @@ def run_reference(args, rank):
     dt = time.perf_counter() - t0
     val = samples * args.steps / dt / 1e6
     sample = f"{WIDTH}x{HEIGHT} at {spp_step} spp per step (of the workload's {SPP}); samples/s is spp-independent"
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD, "step_sample": sample},
@@ -346,7 +355,7 @@ def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
                             "scene upload per rank + render + NCCL reduce + resolve + D2H on rank 0"},
             "roofline": roofline, "roofline_hbm": roofline_hbm, "kernel_ms": kernel_ms, "cpu_baseline": cpu_baseline,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 def main():
