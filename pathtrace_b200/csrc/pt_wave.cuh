@@ -258,8 +258,14 @@ PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float 
 // index) as closest_hit<>: the result does not depend on the visiting order.
 //   next(want, idle_mask, ro, rd, t_max, slot, exhausted) -> this lane got a ray   (warp-collective, called by all lanes)
 //   finish(slot, t, id)                                     per lane, when its walk ends (ANY: id >= 0 means occluded)
+#ifndef PT_BVH_MIN_INNER
+#define PT_BVH_MIN_INNER 8
+#endif
 #ifndef PT_BVH_REFILL
 #define PT_BVH_REFILL 16   // measured on C3 / C4: 1 -> 880 / 249 Msamples/s, 8 -> 902 / 275, 16 -> 923 / 283, 32 (no refill) -> 899 / 258
+#endif
+#ifndef PT_BVH_REFILL_L2
+#define PT_BVH_REFILL_L2 24   // the L1/L2 walk with the early loop exit (PT_BVH_MIN_INNER 8), C4: 8 -> 371, 12 -> 383, 16 -> 389, 24 -> 397
 #endif
 constexpr int kWalkDone = -2147483647 - 1;
 template <bool SMEM, bool ANY, class G, class Next, class Finish>
@@ -270,9 +276,10 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
     float tmax = 0.f;
     uint32_t slot = 0;
     bool exhausted = false;
+    constexpr int kMinInner = SMEM ? 0 : PT_BVH_MIN_INNER;
     while (true) {
         const uint32_t idle = __ballot_sync(0xffffffffu, node == kWalkDone);
-        if (exhausted ? idle == 0xffffffffu : __popc(idle) >= PT_BVH_REFILL) {
+        if (exhausted ? idle == 0xffffffffu : __popc(idle) >= (SMEM ? PT_BVH_REFILL : PT_BVH_REFILL_L2)) {
             if (exhausted) break;
             float3 o, d; float tm; uint32_t sl;
             if (next(node == kWalkDone, idle, o, d, tm, sl, exhausted)) {
@@ -280,8 +287,19 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
                 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));   // exact: the slab margins assume IEEE reciprocals
             }
         }
-        // inner nodes: descend until this lane holds a leaf (negative: ~object id) or its stack runs empty
-        while (node >= 0) {
+        // inner nodes: descend until this lane holds a leaf (negative: ~object id) or its stack runs empty.  When the nodes
+        // come through L1/L2 (latency-bound walk) the warp leaves the loop as soon as fewer than PT_BVH_MIN_INNER lanes are
+        // still descending while others hold a leaf: those test their leaves and rejoin the descent instead of idling until
+        // the longest descent ends; the lanes cut short keep their node and resume in the next round.  Measured on C4: 336 ->
+        // 380 Msamples/s (4: 375, 16: 378, 24: 332).  With the nodes in shared memory (C3, compute-bound) the vote per step
+        // costs more than the idle lanes (1005 -> 967), so that walk keeps the per-lane exit.
+        while (true) {
+            if (kMinInner > 0) {
+                const uint32_t inner = __ballot_sync(0xffffffffu, node >= 0);
+                if (inner == 0u) break;
+                if (__popc(inner) < kMinInner && __any_sync(0xffffffffu, node < 0 && node > kWalkDone + 1)) break;
+                if (node < 0) continue;
+            } else if (node < 0) break;
             float4 a, b, c, d;
             g.node(node, a, b, c, d);
             const int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
@@ -297,7 +315,7 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
             else node = sp ? stack[--sp] : kWalkDone + 1;             // kWalkDone + 1: walk over, result not yet written
         }
         // leaves, all lanes together
-        if (node > kWalkDone + 1) {
+        if (node < 0 && node > kWalkDone + 1) {
             const int id = ~node;
             float4 q0, q1, q2;
             g.prim(id, q0, q1, q2);

@@ -120,8 +120,11 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
 // Occupancy: walking the LBVH through L2 (C4) is bound by memory latency and gains from every extra warp (8 CTAs = 32
 // registers per thread, spills included: 290 -> 314 Msamples/s); walking it in shared memory (C3) is compute-bound and loses
 // (934 -> 765), so that one keeps its registers.
+#ifndef PT_STREAM_MINB
+#define PT_STREAM_MINB 8   // resident CTAs per SM asked of the L1/L2 walk (8: 32 registers per thread)
+#endif
 template <bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : 8) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t per_warp) {
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t per_warp) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
     const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
@@ -141,7 +144,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? 1 : 8) k_trace_closest_stream(P
     if (cursor < end) bvh_stream<SMEM, false>(g, t_min, next, finish);
 }
 template <bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : 8) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t per_warp) {
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t per_warp) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
     const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
