@@ -252,20 +252,23 @@ PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float 
 // ---- warp-persistent LBVH traversal with dynamic ray fetch (scenes whose BVH is walked through L1/L2: C3, C4).
 // One thread per ray with a fixed ray per thread leaves most lanes idle on incoherent rays: the warp runs until its longest
 // walk ends and the primitive tests sit inside the node loop (measured on the 1 M-triangle heightfield: 4 of 32 lanes active
-// per instruction).  Here a warp owns a range of the ray queue; lanes descend inner nodes until each holds a leaf, then all
+// per instruction).  Here a warp streams chunks of the ray queue; lanes descend inner nodes until each holds a leaf, then all
 // leaves are tested together (the "while-while" loop of Aila & Laine, HPG 2009), and whenever PT_BVH_REFILL lanes have
-// finished their ray the idle lanes fetch the next rays of the range.  Same tests, same tie rule (equal t -> higher object
+// finished their ray the idle lanes fetch the next rays of the queue.  Same tests, same tie rule (equal t -> higher object
 // index) as closest_hit<>: the result does not depend on the visiting order.
 //   next(want, idle_mask, ro, rd, t_max, slot, exhausted) -> this lane got a ray   (warp-collective, called by all lanes)
 //   finish(slot, t, id)                                     per lane, when its walk ends (ANY: id >= 0 means occluded)
 #ifndef PT_BVH_MIN_INNER
 #define PT_BVH_MIN_INNER 8
 #endif
+#ifndef PT_BVH_MIN_INNER_SMEM
+#define PT_BVH_MIN_INNER_SMEM 8
+#endif
 #ifndef PT_BVH_REFILL
 #define PT_BVH_REFILL 16   // measured on C3 / C4: 1 -> 880 / 249 Msamples/s, 8 -> 902 / 275, 16 -> 923 / 283, 32 (no refill) -> 899 / 258
 #endif
 #ifndef PT_BVH_REFILL_L2
-#define PT_BVH_REFILL_L2 24   // the L1/L2 walk with the early loop exit (PT_BVH_MIN_INNER 8), C4: 8 -> 371, 12 -> 383, 16 -> 389, 24 -> 397
+#define PT_BVH_REFILL_L2 16   // the L1/L2 walk; C4 with static ranges: 8 -> 371, 12 -> 383, 16 -> 389, 24 -> 397; with chunks: 16 -> 468, 24 -> 461
 #endif
 constexpr int kWalkDone = -2147483647 - 1;
 template <bool SMEM, bool ANY, class G, class Next, class Finish>
@@ -276,7 +279,7 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
     float tmax = 0.f;
     uint32_t slot = 0;
     bool exhausted = false;
-    constexpr int kMinInner = SMEM ? 0 : PT_BVH_MIN_INNER;
+    constexpr int kMinInner = SMEM ? PT_BVH_MIN_INNER_SMEM : PT_BVH_MIN_INNER;
     while (true) {
         const uint32_t idle = __ballot_sync(0xffffffffu, node == kWalkDone);
         if (exhausted ? idle == 0xffffffffu : __popc(idle) >= (SMEM ? PT_BVH_REFILL : PT_BVH_REFILL_L2)) {
@@ -287,12 +290,12 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
                 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));   // exact: the slab margins assume IEEE reciprocals
             }
         }
-        // inner nodes: descend until this lane holds a leaf (negative: ~object id) or its stack runs empty.  When the nodes
-        // come through L1/L2 (latency-bound walk) the warp leaves the loop as soon as fewer than PT_BVH_MIN_INNER lanes are
-        // still descending while others hold a leaf: those test their leaves and rejoin the descent instead of idling until
-        // the longest descent ends; the lanes cut short keep their node and resume in the next round.  Measured on C4: 336 ->
-        // 380 Msamples/s (4: 375, 16: 378, 24: 332).  With the nodes in shared memory (C3, compute-bound) the vote per step
-        // costs more than the idle lanes (1005 -> 967), so that walk keeps the per-lane exit.
+        // inner nodes: descend until this lane holds a leaf (negative: ~object id) or its stack runs empty.  The warp leaves
+        // the loop as soon as fewer than kMinInner lanes are still descending while others hold a leaf: those test their
+        // leaves and rejoin the descent instead of idling until the longest descent ends; the lanes cut short keep their
+        // node and resume in the next round.  Measured with static queue ranges: C4 (nodes through L1/L2) 336 -> 380
+        // Msamples/s, C3 (nodes in shared memory, where the vote per step is a tenth of the step) 1005 -> 967; with the
+        // queue handed out in chunks (wavefront.cu: kStreamChunk*) both gain: C3 1279 -> 1320 (4: 1272, 12: 1326, 16: 1302).
         while (true) {
             if (kMinInner > 0) {
                 const uint32_t inner = __ballot_sync(0xffffffffu, node >= 0);

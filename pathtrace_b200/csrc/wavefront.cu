@@ -37,6 +37,10 @@ constexpr int kBlock = 256;
 constexpr int kShadeBlock = PT_SHADE_BLOCK, kShadeMinBlocks = PT_SHADE_MIN_BLOCKS;
 constexpr int kShadeSlots = PT_SHADE_SLOTS;   // path slots owned by one shade CTA (a multiple of kShadeBlock and of kBlock)
 constexpr int kItersPerBatch = 16;
+// queue slots per grab of a stream-traversal warp (divides kShadeSlots).  Measured (C3 shared-memory walk / C4 L2 walk, Msamples/s):
+// static ranges 1004 / 398; chunks of 256: 1153 / 357, 128: 1254 / 426, 64: 1278 / 458, 32: 1223 / 462
+constexpr uint32_t kStreamChunkSmem = 64, kStreamChunkL2 = 32;
+static_assert(PT_SHADE_SLOTS % 64 == 0, "a chunk must lie inside one shadow-queue segment");
 
 // device counter block (uint64 words)
 // device counter block (uint64 words); every counter sits in its own 256-byte line so their L2 atomics do not serialise
@@ -115,8 +119,8 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
     }
 }
 
-// K3 / K5 for scenes that walk the LBVH (pt_wave.cuh: bvh_stream).  A resident grid of warps; warp w owns the slots
-// [w * per_warp, (w + 1) * per_warp) of the queue and streams them through its lanes.
+// K3 / K5 for scenes that walk the LBVH (pt_wave.cuh: bvh_stream).  A resident grid of warps; each takes chunks of
+// kStreamChunk* slots of the queue from a global counter and streams them through its lanes.
 // Occupancy: walking the LBVH through L2 (C4) is bound by memory latency and gains from every extra warp (8 CTAs = 32
 // registers per thread, spills included: 290 -> 314 Msamples/s); walking it in shared memory (C3) is compute-bound and loses
 // (934 -> 765), so that one keeps its registers.
@@ -124,38 +128,55 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
 #define PT_STREAM_MINB 8   // resident CTAs per SM asked of the L1/L2 walk (8: 32 registers per thread)
 #endif
 template <bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t per_warp) {
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t chunk, unsigned long long* __restrict__ next_chunk) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
     const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
-    uint32_t cursor = (blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * per_warp;
-    const uint32_t end = cursor + per_warp < pool.P ? cursor + per_warp : pool.P;
+    // The queue is handed out in chunks from one global counter: a warp whose rays end early takes the next chunk, so all
+    // resident warps stay busy until the queue is empty (a static range per warp left 30 % of the warp slots idle on C4).
+    uint32_t cursor = 0, end = 0;
+    auto grab = [&]() {
+        unsigned long long c = 0;
+        if (lane == 0) c = atomicAdd(next_chunk, (unsigned long long)chunk);
+        c = __shfl_sync(0xffffffffu, c, 0);
+        cursor = c < pool.P ? (uint32_t)c : pool.P;
+        end = cursor + chunk < pool.P ? cursor + chunk : pool.P;
+    };
     auto next = [&](bool want, uint32_t idle, float3& o, float3& d, float& tm, uint32_t& slot, bool& exhausted) {
+        if (cursor >= end) grab();                                   // warp-uniform
         bool got = false;
         const uint32_t i = cursor + __popc(idle & lt);
         if (want && i < end && (pool.meta[i].x >> 31) != 0u) {
             o = v3(pool.ray_o[i]); d = v3(pool.ray_d[i]); tm = __int_as_float(0x7f800000); slot = i; got = true;
         }
         cursor += __popc(idle);
-        exhausted = cursor >= end;
+        exhausted = cursor >= end && end >= pool.P;
         return got;
     };
     auto finish = [&](uint32_t slot, float t, int id) { pool.hit[slot] = make_uint2(__float_as_uint(t), (uint32_t)id); };
-    if (cursor < end) bvh_stream<SMEM, false>(g, t_min, next, finish);
+    bvh_stream<SMEM, false>(g, t_min, next, finish);
 }
 template <bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t per_warp) {
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t chunk,
+                                                                                           unsigned long long* __restrict__ next_chunk) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
     const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
-    uint32_t cursor = (blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5)) * per_warp;
-    const uint32_t end = cursor + per_warp < pool.P ? cursor + per_warp : pool.P;
+    uint32_t cursor = 0, end = 0;                                    // current chunk (a divisor of kShadeSlots: inside one segment)
+    auto grab = [&]() {
+        unsigned long long c = 0;
+        if (lane == 0) c = atomicAdd(next_chunk, (unsigned long long)chunk);
+        c = __shfl_sync(0xffffffffu, c, 0);
+        cursor = c < pool.P ? (uint32_t)c : pool.P;
+        end = cursor + chunk < pool.P ? cursor + chunk : pool.P;
+    };
     // the shadow queue is dense per shade-CTA segment: entries [seg * kShadeSlots, seg * kShadeSlots + seg_count[seg])
     auto next = [&](bool want, uint32_t idle, float3& o, float3& d, float& tm, uint32_t& slot, bool& exhausted) {
         uint32_t take = 0;
-        while (cursor < end) {                                       // warp-uniform: skip the empty tail of a segment
+        while (true) {                                               // warp-uniform: skip chunks in the empty tail of a segment
+            if (cursor >= end) { if (end >= pool.P && end != 0u) break; grab(); if (cursor >= end) break; }
             const uint32_t seg = cursor / kShadeSlots, off = cursor % kShadeSlots, cnt = pool.seg_count[seg];
-            if (off >= cnt) { cursor = (seg + 1) * kShadeSlots; continue; }
+            if (off >= cnt) { cursor = end; continue; }
             take = min(min((uint32_t)__popc(idle), cnt - off), end - cursor);
             break;
         }
@@ -167,7 +188,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_sha
             o = v3(so); d = v3(sd); tm = so.w; slot = i; got = true;
         }
         cursor += take;
-        exhausted = cursor >= end;
+        exhausted = cursor >= end && end >= pool.P;
         return got;
     };
     auto finish = [&](uint32_t slot, float, int id) {
@@ -176,7 +197,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_sha
             atomicAdd(accum + __float_as_uint(pool.sh_d[slot].w), make_float4(c.x, c.y, c.z, 0.f));
         }
     };
-    if (cursor < end) bvh_stream<SMEM, true>(g, t_min, next, finish);
+    bvh_stream<SMEM, true>(g, t_min, next, finish);
 }
 
 // ------------------------------------------------------------------------------------ shade
@@ -571,9 +592,9 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         }
         const int occ = occ_c < occ_s ? occ_c : occ_s;
         if (occ < 1) { ctx->err = "stream traversal kernels do not fit on an SM"; return PT_ERR_CUDA; }
-        stream_grid = (uint32_t)ctx->sm_count * (uint32_t)occ * 2u;   // two waves: a long walk at the end of a range costs half as much
-        const uint32_t n_warps = stream_grid * (kBlock / 32);
-        per_warp = ((P + n_warps - 1) / n_warps + 31) / 32 * 32;
+        stream_grid = (uint32_t)ctx->sm_count * (uint32_t)occ;        // one resident wave; the queue is handed out dynamically
+        static const uint32_t env_chunk = getenv("PT_STREAM_CHUNK") ? (uint32_t)atoi(getenv("PT_STREAM_CHUNK")) : 0u;   // tuning runs
+        per_warp = env_chunk ? env_chunk : mode.smem ? kStreamChunkSmem : kStreamChunkL2;
     }
     const uint32_t sgrid = P / kShadeSlots;
     f.chunk = (f.total_work + sgrid - 1) / sgrid;
@@ -602,11 +623,14 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     while (!done) {
         PT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counters + C_SHADOW_BASE, 0, 8 * (C_TOTAL - C_SHADOW_BASE), st));
         for (int it = 0; it < kItersPerBatch; ++it) {
+            // chunk counters of this iteration's two stream launches: words 0 and 1 of its (otherwise unused) shadow line
+            unsigned long long* cur_c = reinterpret_cast<unsigned long long*>(ctx->d_counters + C_SHADOW_BASE + it * C_STRIDE);
+            unsigned long long* cur_s = cur_c + 1;
 #define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
             prof_begin(PT_K_TRACE_CLOSEST);
             if (stream_bvh) {
-                if (mode.smem) k_trace_closest_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, per_warp);
-                else k_trace_closest_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, per_warp);
+                if (mode.smem) k_trace_closest_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, per_warp, cur_c);
+                else k_trace_closest_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, per_warp, cur_c);
             } else PT_DISPATCH(mode, TRACE);
             prof_end();
 #undef TRACE
@@ -618,8 +642,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
                 prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
                 if (stream_bvh) {
-                    if (mode.smem) k_trace_shadow_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, per_warp);
-                    else k_trace_shadow_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, per_warp);
+                    if (mode.smem) k_trace_shadow_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, per_warp, cur_s);
+                    else k_trace_shadow_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, per_warp, cur_s);
                 } else PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
                 prof_end();
