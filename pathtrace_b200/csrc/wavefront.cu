@@ -578,7 +578,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     // per slot (A/B runs)
     static const bool no_stream = getenv("PT_NO_STREAM_BVH") != nullptr;
     const bool stream_bvh = !mode.brute && scene.n_objects >= 2 && !no_stream;
-    uint32_t stream_grid = 0, per_warp = 0;
+    uint32_t stream_grid = 0, stream_chunk = 0;
     if (stream_bvh) {
         int occ_c = 0, occ_s = 0;
         if (mode.smem) {
@@ -594,7 +594,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         if (occ < 1) { ctx->err = "stream traversal kernels do not fit on an SM"; return PT_ERR_CUDA; }
         stream_grid = (uint32_t)ctx->sm_count * (uint32_t)occ;        // one resident wave; the queue is handed out dynamically
         static const uint32_t env_chunk = getenv("PT_STREAM_CHUNK") ? (uint32_t)atoi(getenv("PT_STREAM_CHUNK")) : 0u;   // tuning runs
-        per_warp = env_chunk ? env_chunk : mode.smem ? kStreamChunkSmem : kStreamChunkL2;
+        stream_chunk = env_chunk ? env_chunk : mode.smem ? kStreamChunkSmem : kStreamChunkL2;
     }
     const uint32_t sgrid = P / kShadeSlots;
     f.chunk = (f.total_work + sgrid - 1) / sgrid;
@@ -629,8 +629,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
             prof_begin(PT_K_TRACE_CLOSEST);
             if (stream_bvh) {
-                if (mode.smem) k_trace_closest_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, per_warp, cur_c);
-                else k_trace_closest_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, per_warp, cur_c);
+                if (mode.smem) k_trace_closest_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c);
+                else k_trace_closest_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, stream_chunk, cur_c);
             } else PT_DISPATCH(mode, TRACE);
             prof_end();
 #undef TRACE
@@ -642,8 +642,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
                 prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
                 if (stream_bvh) {
-                    if (mode.smem) k_trace_shadow_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, per_warp, cur_s);
-                    else k_trace_shadow_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, per_warp, cur_s);
+                    if (mode.smem) k_trace_shadow_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s);
+                    else k_trace_shadow_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s);
                 } else PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
                 prof_end();
