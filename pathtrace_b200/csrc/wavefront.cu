@@ -121,11 +121,12 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
 
 // K3 / K5 for scenes that walk the LBVH (pt_wave.cuh: bvh_stream).  A resident grid of warps; each takes chunks of
 // kStreamChunk* slots of the queue from a global counter and streams them through its lanes.
-// Occupancy: walking the LBVH through L2 (C4) is bound by memory latency and gains from every extra warp (8 CTAs = 32
-// registers per thread, spills included: 290 -> 314 Msamples/s); walking it in shared memory (C3) is compute-bound and loses
-// (934 -> 765), so that one keeps its registers.
+// Occupancy of the walk through L1/L2 (C4, bound by memory latency).  With a static range per warp every extra warp helped
+// (8 CTAs = 32 registers per thread with ~100 bytes of spills: 290 -> 314 Msamples/s); with the queue handed out in chunks
+// the spill traffic in the dependent chain costs more than the warps hide: 8 CTAs 465, 7: 468, 6 (40 registers): 477,
+// 5 (48 registers, no spills): 512.  Walking the tree in shared memory (C3) is compute-bound and keeps its registers.
 #ifndef PT_STREAM_MINB
-#define PT_STREAM_MINB 8   // resident CTAs per SM asked of the L1/L2 walk (8: 32 registers per thread)
+#define PT_STREAM_MINB 5   // resident CTAs per SM asked of the L1/L2 walk
 #endif
 template <bool SMEM>
 __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t chunk, unsigned long long* __restrict__ next_chunk) {
