@@ -249,6 +249,7 @@ struct World {                                         // :54-62
             pt_camera cam = camera.describe();
             pt_render_params p; std::memset(&p, 0, sizeof p);
             p.spp = opt.sample_num; p.sample_offset = opt.sample_offset; p.min_depth = opt.min_depth; p.max_depth = opt.max_depth;
+            p.n_light_samples = 1;                                                                                  // NUM_LIGHT_SAMPLES, rendering.rs:10
             p.strategy = (uint32_t)opt.strategy; p.traversal = PT_TRAVERSAL_AUTO; p.seed = opt.seed; p.t_min = 0.001f;
             const size_t npix = (size_t)cam.width * cam.height;
             std::vector<float> rad(npix * 3); std::vector<uint8_t> rgba(npix * 4);

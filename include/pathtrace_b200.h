@@ -47,25 +47,36 @@ typedef struct {
 } pt_camera;
 
 /* Compile-time constants / cargo features of the reference turned into run-time fields:
- * SAMPLE_NUM world.rs:18; MIN_DEPTH/MAX_DEPTH rendering.rs:6-7; features mis|brdf_only Cargo.toml:6-10. */
+ * SAMPLE_NUM world.rs:18; MIN_DEPTH/MAX_DEPTH/NUM_LIGHT_SAMPLES rendering.rs:6-10; features mis|brdf_only Cargo.toml:6-10. */
 enum { PT_STRATEGY_MIS = 0, PT_STRATEGY_BRDF_ONLY = 1 };
-enum { PT_TRAVERSAL_AUTO = 0, PT_TRAVERSAL_BVH = 1, PT_TRAVERSAL_BRUTE = 2 };
+/* How hit_scene (world.rs:270-290) is evaluated.  Every value returns the same closest hit (id and t bit-equal, tie rule
+ * included).
+ *   AUTO        <= 16 objects: BRUTE; more: BVH
+ *   BVH         GPU-built LBVH
+ *   BRUTE       linear scan in object order like the reference; the library picks the fastest bit-exact form the scene allows
+ *               (triangle pairs from the constant bank, unchecked reciprocal inside the FP32 coordinate domain)
+ *   BRUTE_TABLE the scan table from shared memory with every range check (the conservative form of BRUTE)
+ *   BRUTE_PARAM_CHECKED  the constant-bank scan with every range check */
+enum { PT_TRAVERSAL_AUTO = 0, PT_TRAVERSAL_BVH = 1, PT_TRAVERSAL_BRUTE = 2, PT_TRAVERSAL_BRUTE_TABLE = 3, PT_TRAVERSAL_BRUTE_PARAM_CHECKED = 4,
+       PT_TRAVERSAL_COUNT = 5 };
 typedef struct {
-    uint32_t spp;            /* samples per pixel rendered by THIS call */
-    uint32_t sample_offset;  /* global index of the first sample (spp split across GPUs / progressive chunks) */
-    uint32_t min_depth;      /* 4  */
-    uint32_t max_depth;      /* 50 (soft: extra 0.5^(depth-4) roulette factor beyond it, rendering.rs:93-95) */
-    uint32_t strategy;       /* PT_STRATEGY_* */
-    uint32_t traversal;      /* PT_TRAVERSAL_* */
-    uint64_t seed;           /* Philox key */
-    float t_min;             /* 0.001 (rendering.rs:41,:64,:105) */
-    uint32_t path_pool;      /* wavefront pool size in paths; 0 = default */
-    uint32_t flags;          /* PT_FLAG_* */
+    uint32_t spp;              /* samples per pixel rendered by THIS call */
+    uint32_t sample_offset;    /* global index of the first sample (spp split across GPUs / progressive chunks); offset + spp <= 2^24 */
+    uint32_t min_depth;        /* 4; <= 254 (the path state keeps the depth in 8 bits; paths are cut at depth 254) */
+    uint32_t max_depth;        /* 50 (soft: extra 0.5^(depth-4) roulette factor beyond it, rendering.rs:93-95) */
+    uint32_t n_light_samples;  /* NUM_LIGHT_SAMPLES, rendering.rs:10: the reference's constant 1; 0 means 1; anything else is PT_ERR_INVALID */
+    uint32_t strategy;         /* PT_STRATEGY_* */
+    uint32_t traversal;        /* PT_TRAVERSAL_* */
+    uint32_t flags;            /* PT_FLAG_* */
+    uint64_t seed;             /* Philox key */
+    float t_min;               /* 0.001 (rendering.rs:41,:64,:105); finite, >= 0 */
+    uint32_t path_pool;        /* wavefront pool size in paths; 0 = default */
 } pt_render_params;
 enum {
-    PT_FLAG_PROFILE = 1,    /* time every kernel launch with CUDA events into pt_stats.ms_kernel (slower) */
-    PT_FLAG_HBM_QUEUES = 2  /* force the HBM-queue wavefront (one launch per stage per bounce) even when the scene is small
-                               enough for the shared-memory wavefront (one persistent launch per frame) */
+    PT_FLAG_PROFILE = 1,     /* time every kernel launch with CUDA events into pt_stats.ms_kernel (slower) */
+    PT_FLAG_HBM_QUEUES = 2,  /* force the HBM-queue wavefront (one launch per stage per bounce) even when the scene is small
+                                enough for the shared-memory wavefront (one persistent launch per frame) */
+    PT_FLAG_COUNTERS = 4     /* count LBVH node visits and primitive tests into the stats of the HBM-queue wavefront (slower) */
 };
 enum { PT_K_GENERATE = 0, PT_K_TRACE_CLOSEST = 1, PT_K_SHADE = 2, PT_K_TRACE_SHADOW = 3, PT_K_SMEM_WAVEFRONT = 4, PT_K_COUNT = 5 };
 
@@ -75,18 +86,22 @@ typedef struct {
     uint64_t path_vertices;     /* shade invocations on non-emissive hits */
     uint64_t wavefront_iters;   /* wavefront iterations */
     uint64_t kernel_launches;   /* kernels launched by this call */
+    uint64_t nodes_visited;     /* PT_FLAG_COUNTERS: LBVH nodes fetched (64 B each), closest + shadow walks */
+    uint64_t prim_tests;        /* PT_FLAG_COUNTERS: primitive records fetched and tested (48 B each) */
     float ms_total;             /* device time of the call, CUDA events */
     float ms_upload, ms_render, ms_download;
     float ms_kernel[5];         /* PT_FLAG_PROFILE only: summed CUDA-event time per kernel class (PT_K_*) */
     uint32_t n_kernel[5];       /* launches per kernel class */
     uint32_t path_pool;         /* pool size actually used */
     float phase_share[3];       /* PT_FLAG_PROFILE, shared-memory wavefront: share of warp cycles in closest-hit items, shading (+ shadow ray) items, waiting */
+    uint32_t scan_mode;         /* shared-memory wavefront: 0 LBVH, 1 scan table, 2 constant-bank scan (checked), 3 constant-bank scan (in-domain); 0xffffffff otherwise */
 } pt_stats;
 
 typedef struct pt_context pt_context;
 typedef struct pt_scene pt_scene;
 
-/* Binds one CUDA device (one process per GPU; multi-GPU = one context per rank + a reduce of the sum buffer). */
+/* Binds one CUDA device.  Multi-GPU: either one context per process and rank with the caller reducing the sum buffers
+ * (pt_render_accumulate_device / pt_resolve_device; what bench.py does under torchrun), or pt_group_* below. */
 int32_t pt_context_create(int32_t device_id, pt_context** out);
 void pt_context_destroy(pt_context* ctx);
 const char* pt_last_error(const pt_context* ctx_or_null);
@@ -101,6 +116,16 @@ void pt_scene_destroy(pt_scene* scene);
  *   rgba8:        W*H*4 bytes, sqrt gamma, clamp, *255 truncated, alpha 255 (== World.data, world.rs:321-332) */
 int32_t pt_render(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p,
                   float* radiance_rgb, uint8_t* rgba8, pt_stats* stats_or_null);
+
+/* pt_render plus the second moment the per-pixel z-test needs (sits beside the sum of world.rs:296-313).  The spp
+ * samples are rendered as `batches` consecutive batches of spp / batches samples (batches must divide spp); batch b's per-pixel
+ * radiance SUM S_b goes into the frame sum and S_b^2 into the second moment:
+ *   radiance_rgb = (sum_b S_b) / spp              moment2_rgb = sum_b S_b^2          (both W*H*3 floats)
+ * batches == spp gives the literal per-sample sum of squares; with B batches the variance of the mean is estimated as
+ * (moment2 / B - (spp * radiance / B)^2) / (B - 1) / (spp / B)^2 with B - 1 degrees of freedom.  Same samples as one
+ * pt_render call of spp samples (the RNG is keyed by the global sample index). */
+int32_t pt_render_moments(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, uint32_t batches,
+                          float* radiance_rgb, float* moment2_rgb, pt_stats* stats_or_null);
 
 /* Device-resident variant for the multi-GPU spp split: ADDS this call's samples into d_accum (device pointer,
  * W*H float4 = {sum r, sum g, sum b, reserved}); caller zeroes it, reduces it across ranks and resolves it. */
@@ -124,6 +149,27 @@ int32_t pt_bvh_download(pt_context* ctx, const pt_scene* scene, uint32_t* codes_
                         float* bounds);
 uint32_t pt_scene_num_objects(const pt_scene* scene);
 uint32_t pt_scene_num_lights(const pt_scene* scene);
+/* Device time (CUDA events) pt_scene_create spent packing the scene and building the LBVH, and the kernels it launched. */
+float pt_scene_build_ms(const pt_scene* scene);
+uint32_t pt_scene_build_launches(const pt_scene* scene);
+
+/* Multi-GPU through the C ABI: one host process drives n devices.  The path shards by samples per pixel:
+ * device g renders the whole frame for the global sample indices [off_g, off_g + spp_g) (spp_g = spp / n, the first spp % n
+ * devices one more), scene and LBVH are replicated, and ONE ncclReduce(sum, float32, root = device_ids[0]) of the W*H float4
+ * sum buffer combines them; the root resolves (world.rs:315-332).  NCCL is loaded at run time (libnccl.so.2); a group of one
+ * device needs no NCCL.  pt_group_render blocks until the root's results are in the caller's buffers; stats (may be null) are
+ * the sums over devices, ms_total the wall time of the slowest one. */
+typedef struct pt_group pt_group;
+typedef struct pt_group_scene pt_group_scene;
+int32_t pt_group_create(const int32_t* device_ids, int32_t n, pt_group** out);
+void pt_group_destroy(pt_group* g);
+int32_t pt_group_size(const pt_group* g);
+pt_context* pt_group_context(pt_group* g, int32_t i);
+const char* pt_group_last_error(const pt_group* g_or_null);
+int32_t pt_group_scene_create(pt_group* g, const pt_shape* shapes, const pt_material* materials, uint32_t n_objects, pt_group_scene** out);
+void pt_group_scene_destroy(pt_group_scene* scene);
+int32_t pt_group_render(pt_group* g, const pt_group_scene* scene, const pt_camera* cam, const pt_render_params* p,
+                        float* radiance_rgb, uint8_t* rgba8, pt_stats* stats_or_null);
 
 /* world.rs:344-369 — writes luminance.csv byte-compatibly ("x,y,r,g,b,luminance", {:.6}) from a radiance buffer. */
 int32_t pt_export_luminance(const char* path, const float* radiance_rgb, uint32_t width, uint32_t height);

@@ -5,14 +5,18 @@
 // legs may build, link or call anything under oracle/.  The CUDA product under
 // pathtrace_b200/csrc/ never includes this file.
 //
-// PARITY STATUS: "parity unpinned" for everything except the Vector3 operators.  The reference's
-// own tests (src/math.rs:246-418) pin only Vector3 arithmetic; those known answers are replayed
-// in tests/test_oracle_kat.py.  Nothing in the reference pins intersection, sampling, materials,
-// integrator or image (its world.rs tests have no assertions and do not compile), and the
-// reference cannot be built here (no rustc/cargo, needs a window).  The restatement below,
-// reviewed against the cited line ranges, is therefore the oracle; its internal-consistency
-// tests (recursive == iterative, pdf normalisation, brute force == BVH) guard it.
-//
+// PARITY STATUS: "parity unpinned".  The reference's own tests (src/math.rs:246-418) pin only Vector3
+// arithmetic; those known answers are replayed in tests/test_oracle_kat.py.  Nothing in the
+// reference pins intersection, sampling, materials, integrator or image (its world.rs tests have
+// no assertions and do not compile), and the reference cannot be built here (no rustc/cargo,
+// needs a window).  What guards this restatement instead (all in the CPU suite):
+//   tests/test_oracle_pinning.py  independent NumPy f64 transcriptions of shape.rs / material.rs /
+//                                 mirror.rs written in the test file from the Rust lines and compared
+//                                 with this code to 1e-12; every sampler's pdf integrates to one and
+//                                 its sample histogram follows its pdf; white-furnace energy
+//                                 conservation; reciprocity of the GGX reflection lobe
+//   tests/test_oracle_kat.py      Vector3 + Philox known answers; recursive == iterative
+//   tests/test_golden.py          committed outputs (drift guard)
 // Third-party arithmetic absent from /root/reference: rand 0.9.2 / rand_chacha 0.9.0 /
 // rand_core 0.9.3 (Cargo.lock:1092-1115; StdRng = ChaCha12).  Not restated: the north star
 // mandates a counter-based RNG, so image parity is distributional.  The RNG here is
@@ -254,14 +258,15 @@ template <class T> struct HitRecord {
 // kind 1 = TriangleShape{v0,v1,v2} (:148-152).
 // ----------------------------------------------------------------------------------------------
 enum : uint32_t { SHAPE_SPHERE = 0, SHAPE_TRIANGLE = 1 };
-struct ShapeDesc { uint32_t kind; float v[9]; };   // mirrors pt_shape
+struct ShapeDesc { uint32_t kind; float v[9]; };    // mirrors pt_shape (what crosses the C ABI: f32)
+struct ShapeDescD { uint32_t kind; double v[9]; };  // the reference's own f64 scene data (world.rs:80-211 builds from f64 literals)
 
 template <class T> struct SurfaceSample { Vec3<T> point, normal; T pdf_omega; Vec3<T> light_dir; T d; };
 
 template <class T> struct Shape {
     uint32_t kind;
     Vec3<T> a, b, c;   // sphere: a = center, b.x = radius; triangle: v0, v1, v2
-    explicit Shape(const ShapeDesc& s) : kind(s.kind) {
+    template <class SD> explicit Shape(const SD& s) : kind(s.kind) {
         a = Vec3<T>(T((double)s.v[0]), T((double)s.v[1]), T((double)s.v[2]));
         b = Vec3<T>(T((double)s.v[3]), T((double)s.v[4]), T((double)s.v[5]));
         c = Vec3<T>(T((double)s.v[6]), T((double)s.v[7]), T((double)s.v[8]));
@@ -404,7 +409,8 @@ template <class T> struct Shape {
 // kind 3 OrenNayar{albedo,roughness,a,b}             p = [albedo.xyz, roughness, a, b]
 // ----------------------------------------------------------------------------------------------
 enum : uint32_t { MAT_LAMBERT = 0, MAT_EMISSIVE = 1, MAT_MIRROR = 2, MAT_ORENNAYAR = 3 };
-struct MaterialDesc { uint32_t kind; float p[8]; };   // mirrors pt_material
+struct MaterialDesc { uint32_t kind; float p[8]; };    // mirrors pt_material
+struct MaterialDescD { uint32_t kind; double p[8]; };  // f64 parameters as the reference holds them
 
 template <class T> struct BsdfSample { Vec3<T> dir, f; T pdf, cos_theta; };
 template <class T> struct BsdfEval { Vec3<T> f; T pdf; };
@@ -432,7 +438,7 @@ template <class T> struct Material {
     uint32_t kind;
     Vec3<T> color;          // albedo / emission / Mirror.color
     T roughness, metallic, ior, on_a, on_b;
-    explicit Material(const MaterialDesc& m) : kind(m.kind), roughness(T(0)), metallic(T(0)), ior(T(1)), on_a(T(1)), on_b(T(0)) {
+    template <class MD> explicit Material(const MD& m) : kind(m.kind), roughness(T(0)), metallic(T(0)), ior(T(1)), on_a(T(1)), on_b(T(0)) {
         auto P = [&](int i) { return T((double)m.p[i]); };
         switch (kind) {
             case MAT_LAMBERT: case MAT_EMISSIVE: color = Vec3<T>(P(0), P(1), P(2)); break;
@@ -640,7 +646,7 @@ template <class T> struct World {
     RenderParams prm;
     T t_min;
 
-    World(const CameraDesc& cam, const ShapeDesc* sh, const MaterialDesc* mt, uint32_t n, const RenderParams& p)
+    template <class SD, class MD> World(const CameraDesc& cam, const SD* sh, const MD* mt, uint32_t n, const RenderParams& p)
         : camera(cam), prm(p), t_min(T((double)p.t_min)) {
         for (uint32_t i = 0; i < n; ++i) { shapes.emplace_back(sh[i]); materials.emplace_back(mt[i]); }
         // world.rs:214-225: a light is any object whose emit() has non-zero length
@@ -759,7 +765,7 @@ template <class T> struct World {
 
     // ---- Iterative form of both strategies: the shape the GPU executes ---
     // No re-trace (Q8); radiance accumulated as beta-weighted sums.  Must agree with the recursive
-    // form sample-for-sample up to floating-point re-association (tests/test_oracle_consistency.py).
+    // form sample-for-sample up to floating-point re-association (tests/test_oracle_kat.py: test_recursive_equals_iterative).
     Vec3<T> radiance_iterative(Ray<T> ray, const RngKey& rng, RayCounters* rc, uint32_t* path_len = nullptr) const {
         const bool mis = prm.strategy == STRATEGY_MIS;
         Vec3<T> beta = Vec3<T>::one(), L = Vec3<T>::zero();

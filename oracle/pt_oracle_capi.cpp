@@ -6,6 +6,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <string>
 
 #include "pt_lbvh_ref.hpp"
 #include "pt_oracle.hpp"
@@ -13,8 +14,8 @@
 using namespace pto;
 
 namespace {
-template <class T>
-void trace_primary_t(const CameraDesc& cam, const ShapeDesc* sh, const MaterialDesc* mt, uint32_t n, const RenderParams& p,
+template <class T, class SD, class MD>
+void trace_primary_t(const CameraDesc& cam, const SD* sh, const MD* mt, uint32_t n, const RenderParams& p,
                      int jitter, float ox, float oy, uint32_t sample, int32_t* obj_id, double* t_out, float* dir_out) {
     World<T> w(cam, sh, mt, n, p);
 #pragma omp parallel for schedule(dynamic, 16)
@@ -34,8 +35,8 @@ void trace_primary_t(const CameraDesc& cam, const ShapeDesc* sh, const MaterialD
         }
 }
 
-template <class T>
-void render_t(const CameraDesc& cam, const ShapeDesc* sh, const MaterialDesc* mt, uint32_t n, const RenderParams& p,
+template <class T, class SD, class MD>
+void render_t(const CameraDesc& cam, const SD* sh, const MD* mt, uint32_t n, const RenderParams& p,
               int recursive, int nthreads, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, double* sum, double* sumsq,
               uint64_t* counters) {
     World<T> w(cam, sh, mt, n, p);
@@ -139,6 +140,101 @@ void pto_sample(int precision, int recursive, const CameraDesc* cam, const Shape
     }
 }
 
+// The same three entry points on the reference's own f64 scene data (ShapeDescD / MaterialDescD): what "the reference's
+// numerics" means literally — world.rs:80-211 builds the scene from f64 literals such as 0.99 and 0.3 that f32 cannot hold.
+void pto_trace_primary_d(int precision, const CameraDesc* cam, const ShapeDescD* sh, const MaterialDescD* mt, uint32_t n,
+                         const RenderParams* p, int jitter, float ox, float oy, uint32_t sample, int32_t* obj_id, double* t, float* dir_out) {
+    if (precision == 0) trace_primary_t<double>(*cam, sh, mt, n, *p, jitter, ox, oy, sample, obj_id, t, dir_out);
+    else trace_primary_t<float>(*cam, sh, mt, n, *p, jitter, ox, oy, sample, obj_id, t, dir_out);
+}
+double pto_render_d(int precision, int recursive, const CameraDesc* cam, const ShapeDescD* sh, const MaterialDescD* mt, uint32_t n,
+                    const RenderParams* p, int nthreads, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, double* sum, double* sumsq,
+                    uint64_t* counters) {
+    auto t0 = std::chrono::steady_clock::now();
+    if (precision == 0) render_t<double>(*cam, sh, mt, n, *p, recursive, nthreads, x0, y0, x1, y1, sum, sumsq, counters);
+    else render_t<float>(*cam, sh, mt, n, *p, recursive, nthreads, x0, y0, x1, y1, sum, sumsq, counters);
+    return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+void pto_sample_d(int precision, int recursive, const CameraDesc* cam, const ShapeDescD* sh, const MaterialDescD* mt, uint32_t n,
+                  const RenderParams* p, uint32_t x, uint32_t y, uint32_t sample, double rgb[3]) {
+    if (precision == 0) {
+        World<double> w(*cam, sh, mt, n, *p);
+        Vec3<double> c = w.sample_radiance(x, y, sample, recursive != 0, nullptr);
+        rgb[0] = c.x; rgb[1] = c.y; rgb[2] = c.z;
+    } else {
+        World<float> w(*cam, sh, mt, n, *p);
+        Vec3<float> c = w.sample_radiance(x, y, sample, recursive != 0, nullptr);
+        rgb[0] = c.x; rgb[1] = c.y; rgb[2] = c.z;
+    }
+}
+
+}  // extern "C"
+
+// ---- unit hooks for tests/test_oracle_pinning.py: one shape / material routine per call, f64 in and out ----------------------
+namespace {
+template <class T> Vec3<T> vin(const double v[3]) { return Vec3<T>(T(v[0]), T(v[1]), T(v[2])); }
+template <class T> void vout(const Vec3<T>& v, double o[3]) { o[0] = to_double(v.x); o[1] = to_double(v.y); o[2] = to_double(v.z); }
+template <class T> Ray<T> ray_in(const double ro[3], const double rd[3], double eta) {
+    Ray<T> r(vin<T>(ro), vin<T>(rd));   // Ray::new normalises, camera.rs:10-16
+    r.eta_ratio = T(eta);
+    return r;
+}
+template <class T>
+void bsdf_pdf_t(const MaterialDescD& m, const double rd[3], double eta, const double o[3], const double n[3], double f[3], double* pdf) {
+    const double zero[3] = {0, 0, 0};
+    BsdfEval<T> e = Material<T>(m).bsdf_pdf(ray_in<T>(zero, rd, eta), vin<T>(o), vin<T>(n));
+    vout(e.f, f); *pdf = to_double(e.pdf);
+}
+template <class T>
+void bsdf_sample_t(const MaterialDescD& m, const double rd[3], double eta, const double n[3], double r1, double r2, double r3, double dir[3],
+                   double f[3], double* pdf, double* cos_theta) {
+    const double zero[3] = {0, 0, 0};
+    BsdfSample<T> s = Material<T>(m).bsdf_pdf_sample(ray_in<T>(zero, rd, eta), vin<T>(n), T(r1), T(r2), T(r3));
+    vout(s.dir, dir); vout(s.f, f); *pdf = to_double(s.pdf); *cos_theta = to_double(s.cos_theta);
+}
+template <class T>
+int shape_hit_t(const ShapeDescD& sd, const double ro[3], const double rd[3], double t_min, double t_max, double* t, double point[3], double normal[3],
+                int* front) {
+    HitRecord<T> h;
+    if (!Shape<T>(sd).hit(ray_in<T>(ro, rd, 1.0), T(t_min), T(t_max), h)) return 0;
+    *t = to_double(h.t); vout(h.point, point); vout(h.normal, normal); *front = h.front_face ? 1 : 0;
+    return 1;
+}
+template <class T>
+void shape_sample_t(const ShapeDescD& sd, const double from[3], const double* target, double r1, double r2, double point[3], double normal[3],
+                    double* pdf_omega, double ldir[3], double* d) {
+    HitRecord<T> hf, ht;
+    hf.point = vin<T>(from);
+    if (target) ht.point = vin<T>(target);
+    SurfaceSample<T> s = Shape<T>(sd).sample_surface_from_point(hf, target ? &ht : nullptr, T(r1), T(r2));
+    vout(s.point, point); vout(s.normal, normal); *pdf_omega = to_double(s.pdf_omega); vout(s.light_dir, ldir); *d = to_double(s.d);
+}
+}  // namespace
+extern "C" {
+// Material::bsdf_pdf (material.rs:86-91, :139-148, :226-266; mirror.rs:179-198).  rd = incoming ray direction.
+void pto_bsdf_pdf(int precision, const MaterialDescD* m, const double rd[3], double eta, const double o[3], const double n[3], double f[3],
+                  double* pdf) {
+    if (precision == 0) bsdf_pdf_t<double>(*m, rd, eta, o, n, f, pdf); else bsdf_pdf_t<float>(*m, rd, eta, o, n, f, pdf);
+}
+// Material::bsdf_pdf_sample (material.rs:29-40; mirror.rs:200-305); r1, r2, r3 = the uniforms in the reference's draw order.
+void pto_bsdf_pdf_sample(int precision, const MaterialDescD* m, const double rd[3], double eta, const double n[3], double r1, double r2,
+                         double r3, double dir[3], double f[3], double* pdf, double* cos_theta) {
+    if (precision == 0) bsdf_sample_t<double>(*m, rd, eta, n, r1, r2, r3, dir, f, pdf, cos_theta);
+    else bsdf_sample_t<float>(*m, rd, eta, n, r1, r2, r3, dir, f, pdf, cos_theta);
+}
+// Shape::hit (shape.rs:53-89, :161-198) + HitRecord::new (base.rs:19-34).  Returns 1 on a hit.
+int pto_shape_hit(int precision, const ShapeDescD* s, const double ro[3], const double rd[3], double t_min, double t_max, double* t,
+                  double point[3], double normal[3], int* front) {
+    return precision == 0 ? shape_hit_t<double>(*s, ro, rd, t_min, t_max, t, point, normal, front)
+                          : shape_hit_t<float>(*s, ro, rd, t_min, t_max, t, point, normal, front);
+}
+// Shape::sample_surface_from_point (shape.rs:91-145, :200-242); target == null: sample with (r1, r2); else pdf at that point.
+void pto_shape_sample(int precision, const ShapeDescD* s, const double from[3], const double* target_or_null, double r1, double r2,
+                      double point[3], double normal[3], double* pdf_omega, double ldir[3], double* d) {
+    if (precision == 0) shape_sample_t<double>(*s, from, target_or_null, r1, r2, point, normal, pdf_omega, ldir, d);
+    else shape_sample_t<float>(*s, from, target_or_null, r1, r2, point, normal, pdf_omega, ldir, d);
+}
+
 // Counting-scalar run: iterative form (no redundant re-trace, Q8) over a pixel window.
 // out[0] = flops, out[1] = samples, out[2] = unique rays, out[3] = path vertices,
 // out[4..6] = flops in shading / closest-hit scans / shadow scans, out[7..9] = primary / shadow / scattered rays.
@@ -170,7 +266,17 @@ void pto_tonemap(const double* mean, uint64_t npix, uint8_t* rgba) {
         rgba[4 * i + 3] = 255;
     }
 }
-// world.rs:344-369, byte-compatible with Rust's "{},{},{:.6},{:.6},{:.6},{:.6}"
+}  // extern "C"
+// world.rs:344-369, byte-compatible with Rust's "{},{},{:.6},{:.6},{:.6},{:.6}": fixed notation, 6 decimals, exact decimal
+// expansion rounded half to even (glibc's %.6f does the same); Rust prints non-finite values as NaN, inf, -inf.
+static std::string rust6(double v) {
+    if (std::isnan(v)) return "NaN";
+    if (std::isinf(v)) return v > 0 ? "inf" : "-inf";
+    char buf[400];
+    std::snprintf(buf, sizeof buf, "%.6f", v);
+    return buf;
+}
+extern "C" {
 int pto_export_luminance(const char* path, const double* mean, uint32_t W, uint32_t H) {
     FILE* f = std::fopen(path, "w");
     if (!f) return 1;
@@ -179,7 +285,7 @@ int pto_export_luminance(const char* path, const double* mean, uint32_t W, uint3
         for (uint32_t x = 0; x < W; ++x) {
             const double* v = mean + 3 * ((size_t)y * W + x);
             double lum = 0.2126 * v[0] + 0.7152 * v[1] + 0.0722 * v[2];
-            std::fprintf(f, "%u,%u,%.6f,%.6f,%.6f,%.6f\n", x, y, v[0], v[1], v[2], lum);
+            std::fprintf(f, "%u,%u,%s,%s,%s,%s\n", x, y, rust6(v[0]).c_str(), rust6(v[1]).c_str(), rust6(v[2]).c_str(), rust6(lum).c_str());
         }
     std::fclose(f);
     return 0;

@@ -29,16 +29,17 @@ class pt_camera(C.Structure):
 
 class pt_render_params(C.Structure):
     _fields_ = [("spp", C.c_uint32), ("sample_offset", C.c_uint32), ("min_depth", C.c_uint32), ("max_depth", C.c_uint32),
-                ("strategy", C.c_uint32), ("traversal", C.c_uint32), ("seed", C.c_uint64), ("t_min", C.c_float),
-                ("path_pool", C.c_uint32), ("flags", C.c_uint32)]
+                ("n_light_samples", C.c_uint32), ("strategy", C.c_uint32), ("traversal", C.c_uint32), ("flags", C.c_uint32),
+                ("seed", C.c_uint64), ("t_min", C.c_float), ("path_pool", C.c_uint32)]
 
 
 class pt_stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_scattered", C.c_uint64),
                 ("path_vertices", C.c_uint64), ("wavefront_iters", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("nodes_visited", C.c_uint64), ("prim_tests", C.c_uint64),
                 ("ms_total", C.c_float), ("ms_upload", C.c_float), ("ms_render", C.c_float), ("ms_download", C.c_float),
                 ("ms_kernel", C.c_float * 5), ("n_kernel", C.c_uint32 * 5), ("path_pool", C.c_uint32),
-                ("phase_share", C.c_float * 3)]
+                ("phase_share", C.c_float * 3), ("scan_mode", C.c_uint32)]
 
     def as_dict(self):
         d = {k: getattr(self, k) for k, _ in self._fields_}
@@ -52,12 +53,15 @@ KERNEL_CLASSES = ("generate", "trace_closest", "shade", "trace_shadow", "smem_wa
 
 
 STRATEGY = {"mis": 0, "brdf_only": 1}
-TRAVERSAL = {"auto": 0, "bvh": 1, "brute": 2}
+TRAVERSAL = {"auto": 0, "bvh": 1, "brute": 2, "brute_table": 3, "brute_param_checked": 4}
 
 # every symbol include/pathtrace_b200.h declares
 EXPORTS = ["pt_context_create", "pt_context_destroy", "pt_last_error", "pt_scene_create", "pt_scene_destroy", "pt_render",
-           "pt_render_accumulate_device", "pt_resolve_device", "pt_context_stream", "pt_context_synchronize", "pt_trace_primary",
-           "pt_bvh_download", "pt_scene_num_objects", "pt_scene_num_lights", "pt_export_luminance", "pt_write_ppm", "pt_version", "pt_measure_fp32_peak"]
+           "pt_render_moments", "pt_render_accumulate_device", "pt_resolve_device", "pt_context_stream", "pt_context_synchronize",
+           "pt_trace_primary", "pt_bvh_download", "pt_scene_num_objects", "pt_scene_num_lights", "pt_scene_build_ms",
+           "pt_scene_build_launches", "pt_export_luminance", "pt_write_ppm", "pt_version", "pt_measure_fp32_peak",
+           "pt_group_create", "pt_group_destroy", "pt_group_size", "pt_group_context", "pt_group_last_error",
+           "pt_group_scene_create", "pt_group_scene_destroy", "pt_group_render"]
 
 _lib = None
 
@@ -82,6 +86,18 @@ def load_library() -> C.CDLL:
         lib.pt_scene_num_lights.argtypes = [C.c_void_p]
         lib.pt_scene_num_objects.restype = C.c_uint32
         lib.pt_scene_num_lights.restype = C.c_uint32
+        lib.pt_scene_build_ms.argtypes = [C.c_void_p]
+        lib.pt_scene_build_ms.restype = C.c_float
+        lib.pt_scene_build_launches.argtypes = [C.c_void_p]
+        lib.pt_scene_build_launches.restype = C.c_uint32
+        lib.pt_group_last_error.restype = C.c_char_p
+        lib.pt_group_last_error.argtypes = [C.c_void_p]
+        lib.pt_group_context.restype = C.c_void_p
+        lib.pt_group_context.argtypes = [C.c_void_p, C.c_int32]
+        for name in ("pt_group_destroy", "pt_group_scene_destroy"):
+            getattr(lib, name).restype = None
+            getattr(lib, name).argtypes = [C.c_void_p]
+        lib.pt_group_size.argtypes = [C.c_void_p]
         _lib = lib
     return _lib
 
@@ -101,11 +117,11 @@ def camera_struct(cam: Camera) -> pt_camera:
 
 
 def render_params(spp=3000, sample_offset=0, min_depth=4, max_depth=50, strategy="mis", traversal="auto", seed=0x5EED,
-                  t_min=1e-3, path_pool=0, profile=False, hbm_queues=False) -> pt_render_params:
+                  t_min=1e-3, path_pool=0, profile=False, hbm_queues=False, counters=False, n_light_samples=1) -> pt_render_params:
     s = STRATEGY[strategy] if isinstance(strategy, str) else int(strategy)
     t = TRAVERSAL[traversal] if isinstance(traversal, str) else int(traversal)
-    return pt_render_params(spp, sample_offset, min_depth, max_depth, s, t, seed, t_min, path_pool,
-                            (1 if profile else 0) | (2 if hbm_queues else 0))
+    flags = (1 if profile else 0) | (2 if hbm_queues else 0) | (4 if counters else 0)
+    return pt_render_params(spp, sample_offset, min_depth, max_depth, n_light_samples, s, t, flags, seed, t_min, path_pool)
 
 
 class Context:
@@ -161,6 +177,15 @@ class Scene:
     def n_lights(self):
         return self.ctx.lib.pt_scene_num_lights(self.handle)
 
+    @property
+    def build_ms(self) -> float:
+        """Device time of scene packing + LBVH build inside pt_scene_create (CUDA events)."""
+        return float(self.ctx.lib.pt_scene_build_ms(self.handle))
+
+    @property
+    def build_launches(self) -> int:
+        return int(self.ctx.lib.pt_scene_build_launches(self.handle))
+
     def bvh(self):
         n = self.n_objects
         codes = np.zeros(n, np.uint32); prims = np.zeros(n, np.uint32)
@@ -191,6 +216,25 @@ def render(ctx: Context, scene: Scene, cam: Camera, params: pt_render_params, wa
     return rad, rgba, st.as_dict()
 
 
+def render_moments(ctx: Context, scene: Scene, cam: Camera, params: pt_render_params, batches: int):
+    """pt_render_moments: (radiance [H,W,3], moment2 [H,W,3] = sum over batches of (batch sum)^2, stats)."""
+    H, W = cam.height, cam.width
+    rad = np.empty((H, W, 3), np.float32); m2 = np.empty((H, W, 3), np.float32)
+    st = pt_stats()
+    c = camera_struct(cam)
+    ctx.check(ctx.lib.pt_render_moments(ctx.handle, scene.handle, C.byref(c), C.byref(params), C.c_uint32(batches), _ptr(rad), _ptr(m2), C.byref(st)),
+              "pt_render_moments")
+    return rad, m2, st.as_dict()
+
+
+def variance_of_mean(rad: np.ndarray, m2: np.ndarray, spp: int, batches: int) -> np.ndarray:
+    """Per-pixel variance of the mean radiance from pt_render_moments' outputs (batches - 1 degrees of freedom)."""
+    B, n = batches, spp // batches
+    mean_batch_sum = rad.astype(np.float64) * spp / B
+    var_batch_sum = np.maximum(m2.astype(np.float64) / B - mean_batch_sum ** 2, 0.0) * B / (B - 1)
+    return var_batch_sum / B / n ** 2
+
+
 def render_accumulate_device(ctx: Context, scene: Scene, cam: Camera, params: pt_render_params, d_accum_ptr: int):
     """Adds this call's samples into a device float4 sum buffer (multi-GPU spp split)."""
     st = pt_stats()
@@ -215,6 +259,57 @@ def trace_primary(ctx: Context, scene: Scene, cam: Camera, params: pt_render_par
     ctx.check(ctx.lib.pt_trace_primary(ctx.handle, scene.handle, C.byref(c), C.byref(params), C.c_int32(int(jitter)), C.c_float(ox),
                                        C.c_float(oy), C.c_uint32(sample), _ptr(ids), _ptr(t), _ptr(dirs)), "pt_trace_primary")
     return ids, t, dirs
+
+
+class Group:
+    """pt_group_*: one host process driving several GPUs; spp split + one ncclReduce inside the library."""
+
+    def __init__(self, device_ids):
+        self.lib = load_library()
+        ids = (C.c_int32 * len(device_ids))(*device_ids)
+        h = C.c_void_p()
+        rc = self.lib.pt_group_create(ids, C.c_int32(len(device_ids)), C.byref(h))
+        if rc:
+            raise PathtraceError(f"pt_group_create failed ({rc}): {self.lib.pt_group_last_error(None).decode()}")
+        self.handle = h
+        self.scene = None
+
+    def check(self, rc, what):
+        if rc:
+            raise PathtraceError(f"{what} failed ({rc}): {self.lib.pt_group_last_error(self.handle).decode()}")
+
+    @property
+    def size(self):
+        return self.lib.pt_group_size(self.handle)
+
+    def scene_create(self, shapes, mats):
+        shapes = np.ascontiguousarray(shapes, dtype=SHAPE_DTYPE); mats = np.ascontiguousarray(mats, dtype=MATERIAL_DTYPE)
+        h = C.c_void_p()
+        self.check(self.lib.pt_group_scene_create(self.handle, _ptr(shapes), _ptr(mats), C.c_uint32(shapes.shape[0]), C.byref(h)), "pt_group_scene_create")
+        return h
+
+    def scene_destroy(self, h):
+        self.lib.pt_group_scene_destroy(h)
+
+    def render(self, scene_handle, cam: Camera, params: pt_render_params, want_radiance=True, want_rgba=True):
+        H, W = cam.height, cam.width
+        rad = np.empty((H, W, 3), np.float32) if want_radiance else None
+        rgba = np.empty((H, W, 4), np.uint8) if want_rgba else None
+        st = pt_stats()
+        c = camera_struct(cam)
+        self.check(self.lib.pt_group_render(self.handle, scene_handle, C.byref(c), C.byref(params), _ptr(rad), _ptr(rgba), C.byref(st)), "pt_group_render")
+        return rad, rgba, st.as_dict()
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.pt_group_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def measure_fp32_peak(ctx: Context):

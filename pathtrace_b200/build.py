@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIBDIR = os.path.join(_HERE, "lib")
 LIB = os.environ.get("PT_LIB") or os.path.join(LIBDIR, "libpathtrace_b200.so")   # PT_LIB: development override (kernel variants)
-SOURCES = ["capi.cu", "lbvh.cu", "wavefront.cu", "smem_wavefront.cu"]
+SOURCES = ["capi.cu", "lbvh.cu", "wavefront.cu", "smem_wavefront.cu", "group.cu"]
 HEADERS = ["pt_internal.h", "pt_math.cuh", "pt_shade.cuh", "pt_wave.cuh", os.path.join("..", "..", "include", "pathtrace_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "-ccbin", "g++"]
@@ -62,7 +62,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    r = subprocess.run([nvcc, "-shared", "-ccbin", "g++", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a"],
+    r = subprocess.run([nvcc, "-shared", "-ccbin", "g++", "-o", LIB, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-ldl"],
                        capture_output=True, text=True)
     if r.returncode:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -20,10 +20,23 @@ int keep(pt_context* ctx, int rc) {
     if (rc && ctx) g_last_error = ctx->err;
     return rc;
 }
-bool valid_params(const pt_render_params* p) { return p && p->strategy <= PT_STRATEGY_BRDF_ONLY && p->traversal <= PT_TRAVERSAL_BRUTE && p->t_min >= 0.0f &&
-           (uint64_t)p->sample_offset + p->spp <= (1ull << 24);   // global sample index is packed into 24 bits of the path state
+// NUM_LIGHT_SAMPLES is the compile-time constant 1 in the reference (rendering.rs:10); min_depth must fit the 8-bit depth of
+// the path state (pt_wave.cuh: pack_meta); the global sample index is packed into 24 bits of it.
+bool valid_params(const pt_render_params* p) {
+    return p && p->strategy <= PT_STRATEGY_BRDF_ONLY && p->traversal < PT_TRAVERSAL_COUNT && std::isfinite(p->t_min) && p->t_min >= 0.0f &&
+           p->n_light_samples <= 1 && p->min_depth <= 254 && (uint64_t)p->sample_offset + p->spp <= (1ull << 24);
 }
+const char* kBadParams = "bad render params (strategy / traversal out of range, t_min not finite or negative, n_light_samples > 1, "
+                         "min_depth > 254, or sample_offset + spp > 2^24)";
 bool valid_camera(const pt_camera* c) { return c && c->width >= 2 && c->height >= 2 && (uint64_t)c->width * c->height < (1ull << 31); }
+
+// Rust's `{:.6}` (world.rs:361-365): fixed notation with 6 decimals; non-finite values print as NaN / inf / -inf.
+void fmt6(char* out, size_t n, double v) {
+    if (v != v) std::snprintf(out, n, "NaN");
+    else if (std::isinf(v)) std::snprintf(out, n, v > 0 ? "inf" : "-inf");
+    else std::snprintf(out, n, "%.6f", v);
+}
+}  // namespace
 
 int ensure_frame(pt_context* ctx, size_t npix) {
     if (npix > ctx->accum_px) {
@@ -42,20 +55,9 @@ int ensure_frame(pt_context* ctx, size_t npix) {
     }
     return PT_OK;
 }
-int ensure_pinned(pt_context* ctx, size_t bytes) {
-    if (bytes > ctx->pinned_bytes) {
-        if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
-        ctx->h_pinned = nullptr; ctx->pinned_bytes = 0;
-        PT_CUDA_CHECK(ctx, cudaMallocHost(&ctx->h_pinned, bytes));
-        ctx->pinned_bytes = bytes;
-    }
-    return PT_OK;
-}
-}  // namespace
-
 extern "C" {
 
-const char* pt_version(void) { return "pathtrace_b200 0.1 (sm_100a)"; }
+const char* pt_version(void) { return "pathtrace_b200 0.2 (sm_100a)"; }
 
 const char* pt_last_error(const pt_context* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
 
@@ -92,7 +94,6 @@ void pt_context_destroy(pt_context* ctx) {
     if (ctx->d_rgba) cudaFree(ctx->d_rgba);
     if (ctx->d_counters) cudaFree(ctx->d_counters);
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
-    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->prof_events) cudaEventDestroy(ev);
     cudaStreamDestroy(ctx->stream);
@@ -154,10 +155,15 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
         cudaMemcpyAsync(d_mats, materials, sizeof(pt_material) * n, cudaMemcpyHostToDevice, ctx->stream);
     }
     if (!lights.empty()) cudaMemcpyAsync(sc->dev.light_ids, lights.data(), 4 * lights.size(), cudaMemcpyHostToDevice, ctx->stream);
+    cudaEventRecord(ctx->ev[2], ctx->stream);
     int rc = scene_pack_launch(ctx, d_shapes, d_mats, n, sc->dev);
     if (rc) return cleanup(rc);
-    rc = lbvh_build_device(ctx, d_shapes, n, sc->dev, nullptr);   // synchronises the stream
+    uint64_t launches = n ? (sc->dev.n_brute ? 2 : 1) : 0;
+    rc = lbvh_build_device(ctx, d_shapes, n, sc->dev, &launches);
     if (rc) return cleanup(rc);
+    cudaEventRecord(ctx->ev[3], ctx->stream);
+    if (cudaEventSynchronize(ctx->ev[3]) == cudaSuccess) cudaEventElapsedTime(&sc->build_ms, ctx->ev[2], ctx->ev[3]);
+    sc->build_launches = (uint32_t)launches;
     cleanup(0);
     *out = sc;
     return PT_OK;
@@ -173,12 +179,14 @@ void pt_scene_destroy(pt_scene* sc) {
 
 uint32_t pt_scene_num_objects(const pt_scene* s) { return s ? s->dev.n_objects : 0; }
 uint32_t pt_scene_num_lights(const pt_scene* s) { return s ? s->dev.n_lights : 0; }
+float pt_scene_build_ms(const pt_scene* s) { return s ? s->build_ms : 0.f; }
+uint32_t pt_scene_build_launches(const pt_scene* s) { return s ? s->build_launches : 0; }
 
 int32_t pt_render_accumulate_device(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, void* d_accum,
                                     pt_stats* stats) {
     if (!ctx || !scene || !d_accum) return fail(ctx, PT_ERR_INVALID, "pt_render_accumulate_device: null argument");
     if (!valid_camera(cam)) return fail(ctx, PT_ERR_INVALID, "pt_render: bad camera (width/height must be >= 2)");
-    if (!valid_params(p)) return fail(ctx, PT_ERR_INVALID, "pt_render: bad render params");
+    if (!valid_params(p)) return fail(ctx, PT_ERR_INVALID, std::string("pt_render: ") + kBadParams);
     if (scene->ctx != ctx) return fail(ctx, PT_ERR_INVALID, "pt_render: scene belongs to another context");
     cudaSetDevice(ctx->device);
     if (stats) std::memset(stats, 0, sizeof(*stats));
@@ -202,7 +210,7 @@ int32_t pt_render(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, 
                   pt_stats* stats) {
     if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_render: null argument");
     if (!valid_camera(cam)) return fail(ctx, PT_ERR_INVALID, "pt_render: bad camera (width/height must be >= 2)");
-    if (!valid_params(p) || p->spp == 0) return fail(ctx, PT_ERR_INVALID, "pt_render: bad render params (spp must be > 0)");
+    if (!valid_params(p) || p->spp == 0) return fail(ctx, PT_ERR_INVALID, std::string("pt_render: spp must be > 0; ") + kBadParams);
     cudaSetDevice(ctx->device);
     size_t npix = (size_t)cam->width * cam->height;
     int rc = ensure_frame(ctx, npix);
@@ -228,16 +236,64 @@ int32_t pt_render(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, 
     return PT_OK;
 }
 
+int32_t pt_render_moments(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, uint32_t batches,
+                          float* radiance, float* moment2, pt_stats* stats) {
+    if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_render_moments: null argument");
+    if (!valid_camera(cam)) return fail(ctx, PT_ERR_INVALID, "pt_render_moments: bad camera (width/height must be >= 2)");
+    if (!valid_params(p) || p->spp == 0) return fail(ctx, PT_ERR_INVALID, std::string("pt_render_moments: spp must be > 0; ") + kBadParams);
+    if (batches == 0 || p->spp % batches != 0) return fail(ctx, PT_ERR_INVALID, "pt_render_moments: batches must divide spp");
+    cudaSetDevice(ctx->device);
+    const size_t npix = (size_t)cam->width * cam->height;
+    int rc = ensure_frame(ctx, npix);
+    if (rc) return keep(ctx, rc);
+    DevTemps tmp;
+    float4 *d_batch = nullptr, *d_m2 = nullptr;
+    float* d_m2rgb = nullptr;
+    PT_CUDA_CHECK(ctx, tmp.alloc(&d_batch, sizeof(float4) * npix));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&d_m2, sizeof(float4) * npix));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&d_m2rgb, sizeof(float) * 3 * npix));
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_accum, 0, sizeof(float4) * npix, ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(d_batch, 0, sizeof(float4) * npix, ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(d_m2, 0, sizeof(float4) * npix, ctx->stream));
+    pt_stats total;
+    std::memset(&total, 0, sizeof total);
+    pt_render_params bp = *p;
+    bp.spp = p->spp / batches;
+    for (uint32_t b = 0; b < batches; ++b) {
+        bp.sample_offset = p->sample_offset + b * bp.spp;
+        pt_stats st;
+        rc = pt_render_accumulate_device(ctx, scene, cam, &bp, d_batch, &st);
+        if (rc) return rc;
+        rc = fold_moments_launch(ctx, d_batch, ctx->d_accum, d_m2, (uint32_t)npix);
+        if (rc) return keep(ctx, rc);
+        total.samples += st.samples; total.rays_primary += st.rays_primary; total.rays_shadow += st.rays_shadow;
+        total.rays_scattered += st.rays_scattered; total.path_vertices += st.path_vertices; total.wavefront_iters += st.wavefront_iters;
+        total.kernel_launches += st.kernel_launches + 1; total.ms_render += st.ms_render; total.path_pool = st.path_pool; total.scan_mode = st.scan_mode;
+    }
+    rc = resolve_launch(ctx, ctx->d_accum, cam->width, cam->height, p->spp, ctx->d_radiance, nullptr);
+    if (rc) return keep(ctx, rc);
+    rc = moments_out_launch(ctx, d_m2, (uint32_t)npix, d_m2rgb);
+    if (rc) return keep(ctx, rc);
+    total.kernel_launches += 2;
+    if (radiance) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(radiance, ctx->d_radiance, sizeof(float) * 3 * npix, cudaMemcpyDeviceToHost, ctx->stream));
+    if (moment2) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(moment2, d_m2rgb, sizeof(float) * 3 * npix, cudaMemcpyDeviceToHost, ctx->stream));
+    PT_CUDA_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    total.ms_total = total.ms_render;
+    if (stats) *stats = total;
+    return PT_OK;
+}
+
 int32_t pt_trace_primary(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, int32_t jitter, float ox,
                          float oy, uint32_t sample, int32_t* obj_id, float* t, float* dir) {
     if (!ctx || !scene || !obj_id || !t) return fail(ctx, PT_ERR_INVALID, "pt_trace_primary: null argument");
     if (!valid_camera(cam) || !valid_params(p)) return fail(ctx, PT_ERR_INVALID, "pt_trace_primary: bad camera or params");
     cudaSetDevice(ctx->device);
     size_t npix = (size_t)cam->width * cam->height;
+    DevTemps tmp;
     int32_t* d_obj = nullptr; float *d_t = nullptr, *d_dir = nullptr;
-    PT_CUDA_CHECK(ctx, cudaMalloc(&d_obj, 4 * npix));
-    PT_CUDA_CHECK(ctx, cudaMalloc(&d_t, 4 * npix));
-    if (dir) PT_CUDA_CHECK(ctx, cudaMalloc(&d_dir, 12 * npix));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&d_obj, 4 * npix));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&d_t, 4 * npix));
+    if (dir) PT_CUDA_CHECK(ctx, tmp.alloc(&d_dir, 12 * npix));
     int rc = wavefront_trace_primary(ctx, scene->dev, *cam, *p, jitter, ox, oy, sample, d_obj, d_t, d_dir, nullptr);
     if (!rc) {
         cudaMemcpyAsync(obj_id, d_obj, 4 * npix, cudaMemcpyDeviceToHost, ctx->stream);
@@ -246,7 +302,6 @@ int32_t pt_trace_primary(pt_context* ctx, const pt_scene* scene, const pt_camera
         cudaError_t e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) { ctx->err = std::string("pt_trace_primary: ") + cudaGetErrorString(e); rc = PT_ERR_CUDA; }
     }
-    cudaFree(d_obj); cudaFree(d_t); if (d_dir) cudaFree(d_dir);
     return keep(ctx, rc);
 }
 
@@ -278,7 +333,9 @@ int32_t pt_export_luminance(const char* path, const float* rad, uint32_t W, uint
             const float* v = rad + 3 * ((size_t)y * W + x);
             double r = v[0], g = v[1], b = v[2];
             double lum = 0.2126 * r + 0.7152 * g + 0.0722 * b;
-            std::fprintf(f, "%u,%u,%.6f,%.6f,%.6f,%.6f\n", x, y, r, g, b, lum);
+            char sr[64], sg[64], sb[64], sl[64];
+            fmt6(sr, sizeof sr, r); fmt6(sg, sizeof sg, g); fmt6(sb, sizeof sb, b); fmt6(sl, sizeof sl, lum);
+            std::fprintf(f, "%u,%u,%s,%s,%s,%s\n", x, y, sr, sg, sb, sl);
         }
     std::fclose(f);
     return PT_OK;

@@ -3,7 +3,7 @@
 //
 // The reference has no acceleration structure (src/world.rs:270-290 scans all objects); this replaces
 // that scan.  The build SPEC is in DESIGN.md §LBVH and is restated sequentially by the CPU twin in
-// oracle/pt_lbvh_ref.hpp; tests/test_parity_lbvh.py requires codes, order, topology and boxes to be
+// oracle/pt_lbvh_ref.hpp; tests/test_gpu_parity.py (test_lbvh_bit_exact) requires codes, order, topology and boxes to be
 // bit-exact between the two.  All box arithmetic is min/max (order independent) so the atomics below
 // cannot perturb the result.
 #include <cfloat>
@@ -333,16 +333,17 @@ int lbvh_build_device(pt_context* ctx, const pt_shape* d_shapes, uint32_t n, Sce
     uint64_t nl = 0;
     uint32_t n1 = n ? n : 1;
     out.n_nodes = n > 1 ? n - 1 : 1;
+    DevTemps tmp;   // every temporary below is released on every return path
     float4 *lo = nullptr, *hi = nullptr;
     uint32_t *bounds_ord = nullptr, *keys_a = nullptr, *keys_b = nullptr, *vals_a = nullptr, *vals_b = nullptr, *hist = nullptr;
     float* d_bounds = nullptr;
     int *cl = nullptr, *cr = nullptr;
     uint32_t *pn = nullptr, *pl = nullptr, *flags = nullptr;
-    PT_CUDA_CHECK(ctx, cudaMalloc(&lo, sizeof(float4) * n1));
-    PT_CUDA_CHECK(ctx, cudaMalloc(&hi, sizeof(float4) * n1));
-    PT_CUDA_CHECK(ctx, cudaMalloc(&bounds_ord, 6 * 4));
-    PT_CUDA_CHECK(ctx, cudaMalloc(&d_bounds, 6 * 4));
-    PT_CUDA_CHECK(ctx, cudaMalloc(&out.nodes, sizeof(float4) * 4 * (size_t)out.n_nodes));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&lo, sizeof(float4) * n1));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&hi, sizeof(float4) * n1));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&bounds_ord, 6 * 4));
+    PT_CUDA_CHECK(ctx, tmp.alloc(&d_bounds, 6 * 4));
+    PT_CUDA_CHECK(ctx, cudaMalloc(&out.nodes, sizeof(float4) * 4 * (size_t)out.n_nodes));   // owned by the scene: pt_scene_destroy
     PT_CUDA_CHECK(ctx, cudaMalloc(&out.codes_sorted, 4 * (size_t)n1));
     PT_CUDA_CHECK(ctx, cudaMalloc(&out.prim_sorted, 4 * (size_t)n1));
     const uint32_t init_ord[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
@@ -359,11 +360,11 @@ int lbvh_build_device(pt_context* ctx, const pt_shape* d_shapes, uint32_t n, Sce
         if (n == 1) { PT_CUDA_CHECK(ctx, cudaMemsetAsync(out.codes_sorted, 0, 4, st)); PT_CUDA_CHECK(ctx, cudaMemsetAsync(out.prim_sorted, 0, 4, st)); }
     } else {
         uint32_t nblocks = (n + kSortThreads - 1) / kSortThreads;
-        PT_CUDA_CHECK(ctx, cudaMalloc(&keys_a, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&keys_b, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&vals_a, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&vals_b, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&hist, 4 * (size_t)kRadix * nblocks));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&keys_a, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&keys_b, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&vals_a, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&vals_b, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&hist, 4 * (size_t)kRadix * nblocks));
         k_morton<<<(n + 255) / 256, 256, 0, st>>>(lo, hi, d_bounds, n, keys_a, vals_a); nl++;
         uint32_t *ki = keys_a, *ko = keys_b, *vi = vals_a, *vo = vals_b;
         for (int shift = 0; shift < 32; shift += 4) {   // 8 passes; the top 2 bits are zero (30-bit codes)
@@ -375,19 +376,17 @@ int lbvh_build_device(pt_context* ctx, const pt_shape* d_shapes, uint32_t n, Sce
         }
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(out.codes_sorted, ki, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st));
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(out.prim_sorted, vi, 4 * (size_t)n, cudaMemcpyDeviceToDevice, st));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&cl, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&cr, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&pn, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&pl, 4 * (size_t)n));
-        PT_CUDA_CHECK(ctx, cudaMalloc(&flags, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&cl, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&cr, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&pn, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&pl, 4 * (size_t)n));
+        PT_CUDA_CHECK(ctx, tmp.alloc(&flags, 4 * (size_t)n));
         PT_CUDA_CHECK(ctx, cudaMemsetAsync(flags, 0, 4 * (size_t)n, st));
         k_hierarchy<<<(n - 1 + 255) / 256, 256, 0, st>>>(out.codes_sorted, (int)n, cl, cr, pn, pl); nl++;
         k_refit<<<(n + 255) / 256, 256, 0, st>>>(lo, hi, out.prim_sorted, (int)n, cl, cr, pn, pl, flags, out.nodes); nl++;
     }
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
-    void* tmp[] = {lo, hi, bounds_ord, d_bounds, keys_a, keys_b, vals_a, vals_b, hist, cl, cr, pn, pl, flags};
-    for (void* p : tmp) if (p) cudaFree(p);
     if (launches) *launches += nl;
     return PT_OK;
 }

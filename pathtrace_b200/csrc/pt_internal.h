@@ -43,7 +43,6 @@ struct pt_context {
     // frame buffers owned by the context for pt_render (grown on demand)
     float4* d_accum = nullptr; size_t accum_px = 0;
     float* d_radiance = nullptr; uint8_t* d_rgba = nullptr; size_t out_px = 0;
-    void* h_pinned = nullptr; size_t pinned_bytes = 0;
     uint64_t* d_counters = nullptr;   // device counters block
     uint64_t* h_counters = nullptr;   // pinned mirror
     std::vector<cudaEvent_t> prof_events;   // PT_FLAG_PROFILE: start/stop pairs per launch
@@ -52,8 +51,25 @@ struct pt_context {
 struct pt_scene {
     pt_context* ctx = nullptr;
     SceneDev dev;
+    float build_ms = 0.f;          // scene packing + LBVH build, CUDA events
+    uint32_t build_launches = 0;
 };
 
+// cudaMalloc'd temporaries that are released on every return path
+struct DevTemps {
+    std::vector<void*> ptrs;
+    ~DevTemps() { for (void* p : ptrs) if (p) cudaFree(p); }
+    template <class T> cudaError_t alloc(T** out, size_t bytes) {
+        void* p = nullptr;
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 1);
+        if (e == cudaSuccess) ptrs.push_back(p);
+        *out = static_cast<T*>(p);
+        return e;
+    }
+};
+
+// capi.cu: the context-owned frame buffers (d_accum, d_radiance, d_rgba) hold at least npix pixels afterwards
+int ensure_frame(pt_context* ctx, size_t npix);
 // lbvh.cu
 int lbvh_build_device(pt_context* ctx, const pt_shape* d_shapes, uint32_t n, SceneDev& out, uint64_t* launches);
 // wavefront.cu
@@ -70,6 +86,9 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
 int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
                             float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches);
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba);
+// total += batch; moment2 += batch^2 (per pixel and channel); batch is zeroed for the next one
+int fold_moments_launch(pt_context* ctx, float4* d_batch, float4* d_total, float4* d_moment2, uint32_t npix);
+int moments_out_launch(pt_context* ctx, const float4* d_moment2, uint32_t npix, float* d_out_rgb);
 int fp32_peak_launch(pt_context* ctx, float* tflops, float* ms);
 int scene_pack_launch(pt_context* ctx, const pt_shape* d_shapes, const pt_material* d_mats, uint32_t n, SceneDev& out);
 

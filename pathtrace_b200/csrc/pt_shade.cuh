@@ -179,30 +179,20 @@ PT_DEV float3 orennayar_f(const Mat& m, float3 rd, float3 o, float3 n) {
 PT_DEV void bsdf_eval(const Mat& m, float3 rd, float eta, float3 o, float3 n, float3& f, float& pdf) {
     switch (m.kind) {
         case PT_MATK_LAMBERT: f = m.color * PT_INV_PI; pdf = fmaxf(dot(o, n), 0.0f) * PT_INV_PI; break;
-#ifndef PT_EXPERIMENT_NO_MIRROR
         case PT_MATK_MIRROR: mirror_eval(m, rd, eta, o, n, f, pdf); break;
-#endif
-#ifndef PT_EXPERIMENT_NO_ORENNAYAR
         case PT_MATK_ORENNAYAR: f = orennayar_f(m, rd, o, n); pdf = fmaxf(dot(o, n), 0.0f) * PT_INV_PI; break;
-#endif
         default: f = v3(0.f, 0.f, 0.f); pdf = 1.0f; break;
     }
 }
 // Material::bsdf_pdf_sample (default material.rs:29-40; Mirror override mirror.rs:200-305)
 PT_DEV bool bsdf_sample(const Mat& m, float3 rd, float eta, float3 n, float r1, float r2, float r3, float3& dir, float3& f,
                         float& pdf, float& cos_theta) {
-#ifndef PT_EXPERIMENT_NO_MIRROR
     if (m.kind == PT_MATK_MIRROR) return mirror_sample(m, rd, eta, n, r1, r2, r3, dir, f, pdf, cos_theta);
-#endif
     if (m.kind == PT_MATK_EMISSIVE) return false;   // f = 0: zero throughput (never reached in MIS, rendering.rs:42-49)
     dir = cosine_sample(n, r1, r2);
     cos_theta = fmaxf(dot(dir, n), 0.0f);
     pdf = cos_theta * PT_INV_PI;
-#ifndef PT_EXPERIMENT_NO_ORENNAYAR
     f = m.kind == PT_MATK_LAMBERT ? m.color * PT_INV_PI : orennayar_f(m, rd, dir, n);
-#else
-    f = m.color * PT_INV_PI;
-#endif
     return pdf > 0.0f;
 }
 
@@ -226,11 +216,7 @@ PT_DEV float sphere_pdf_omega(float3 c, float radius, float3 x) {
 // Samples a point on light primitive (q0,q1,q2,q3) as seen from x.  shape.rs:91-145 / :200-242.
 PT_DEV void sample_light_shape(float4 q0, float4 q1, float4 q2, float4 q3, float3 x, float r1, float r2, float3& ldir, float& d,
                                float& pdf_omega) {
-#ifdef PT_EXPERIMENT_NO_SPHERE_LIGHT
-    if (true) {
-#else
     if (__float_as_uint(q0.w) == PT_KIND_TRIANGLE) {
-#endif
         float sq = sqrtf(r1);
         float u = 1.0f - sq, v = r2 * sq;
         float3 p = v3(q0) + v3(q1) * u + v3(q2) * v;

@@ -3,6 +3,8 @@
 // Citations are into /root/reference/src.
 #pragma once
 #include <cfloat>
+#include <cmath>
+#include <cstring>
 
 #include "pt_internal.h"
 #include "pt_shade.cuh"
@@ -12,6 +14,9 @@ using namespace ptd;
 
 constexpr int kStackDepth = 64;
 constexpr uint32_t kMaxSmemPrims = 1024;   // scene staged in shared memory up to this many objects
+constexpr uint32_t kMaxPathDepth = 254;    // the path state keeps the depth in 8 bits (pack_meta): a path that survives roulette this
+                                           // long is cut (rendering.rs:91-98 has no hard cap; with the reference's MAX_DEPTH = 50 the
+                                           // survival probability at depth 254 is below 2^-250)
 
 struct Frame {
     CameraDev cam;
@@ -271,8 +276,11 @@ PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float 
 #define PT_BVH_REFILL_L2 16   // the L1/L2 walk; C4 with static ranges: 8 -> 371, 12 -> 383, 16 -> 389, 24 -> 397; with chunks: 16 -> 468, 24 -> 461
 #endif
 constexpr int kWalkDone = -2147483647 - 1;
-template <bool SMEM, bool ANY, class G, class Next, class Finish>
-PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
+// COUNT: node fetches and primitive tests are counted per lane and added to counters[0] / counters[1] when the warp retires
+// (PT_FLAG_COUNTERS: the numerator of the HBM roofline).
+template <bool SMEM, bool ANY, bool COUNT, class G, class Next, class Finish>
+PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish, unsigned long long* __restrict__ counters = nullptr) {
+    uint32_t n_node_fetch = 0, n_prim_test = 0;
     int node = kWalkDone, sp = 0, best_id = -1;
     int stack[kStackDepth];
     float3 ro = v3(0.f, 0.f, 0.f), rd = ro, inv = ro;
@@ -305,6 +313,7 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
             } else if (node < 0) break;
             float4 a, b, c, d;
             g.node(node, a, b, c, d);
+            if (COUNT) ++n_node_fetch;
             const int cl = __float_as_int(a.w), cr = __float_as_int(b.w);
             float tl, tr;
             const bool hl = slab(v3(a), v3(b), ro, inv, t_min, tmax, tl);
@@ -322,6 +331,7 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
             const int id = ~node;
             float4 q0, q1, q2;
             g.prim(id, q0, q1, q2);
+            if (COUNT) ++n_prim_test;
             const float t = hit_prim(q0, q1, q2, ro, rd, t_min, tmax);
             if (ANY) {
                 if (t >= 0.0f) { best_id = id; sp = 0; }              // occluded: stop this walk
@@ -332,6 +342,11 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish) {
             finish(slot, best_id >= 0 ? tmax : FLT_MAX, best_id);
             node = kWalkDone;
         }
+    }
+    if (COUNT) {
+        n_node_fetch = __reduce_add_sync(0xffffffffu, n_node_fetch);
+        n_prim_test = __reduce_add_sync(0xffffffffu, n_prim_test);
+        if ((threadIdx.x & 31) == 0) { atomicAdd(counters, (unsigned long long)n_node_fetch); atomicAdd(counters + 1, (unsigned long long)n_prim_test); }
     }
 }
 
@@ -457,11 +472,20 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
     // ---- BSDF sample + Russian roulette (rendering.rs:83-102)
     float eta_new = front ? 1.0f / mat_eta(m) : mat_eta(m);   // rendering.rs:20-25
     float3 wo, fs; float pdf, cos_s;
-    bool ok = bsdf_sample(m, rd, eta_new, n, u01(b0.z), u01(b0.w), u01(b1.x), wo, fs, pdf, cos_s);
+    const bool sampled = bsdf_sample(m, rd, eta_new, n, u01(b0.z), u01(b0.w), u01(b1.x), wo, fs, pdf, cos_s);
     float3 tn = beta * fs * (cos_s / pdf);
-    ok = ok && finite3(tn);
-    float q = ok ? rr_prob(f, tn, depth) : 0.0f;
-    if (!ok || u01(b1.y) > q) {
+    const bool ok = sampled && finite3(tn);
+    if (!ok) {
+        // Mirror's failure tuple (normal, 0, pdf = 1, cos = 0), mirror.rs:214-217 / :258-265 / :293-300: next_throughput is zero,
+        // so before the roulette depth (q == 1, rendering.rs:91-92) the reference keeps this vertex's direct light and nothing
+        // after it; from the roulette depth on q == 0 kills the path together with its direct light (Q1).  A non-positive pdf of
+        // the cosine-weighted samplers ends the path without its direct light (documented deviation).
+        o.finished = true;
+        if (!sampled && m.kind == PT_MATK_MIRROR && depth < f.min_depth && want_shadow) { o.emit_shadow = true; o.new_ro = make_float4(p.x, p.y, p.z, eta_new); }
+        return o;
+    }
+    float q = rr_prob(f, tn, depth);
+    if (u01(b1.y) > q || depth >= kMaxPathDepth) {
         o.finished = true;                                  // D of this vertex is dropped too (Q1)
         return o;
     }
@@ -480,6 +504,24 @@ inline SceneView make_scene_view(const SceneDev& d) {
     v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
     v.brute = d.brute; v.n_brute = d.n_brute; v.n_pairs = d.n_pairs;
     return v;
+}
+// Which form of the brute-force scan a scene / camera / PT_TRAVERSAL_* value gets (pt_stats.scan_mode): 1 = scan table from
+// shared memory, checked pair test; 2 = triangle pairs from the constant bank, checked; 3 = constant bank, in-domain (no
+// reciprocal range check, no `u <= 1`: pt_math.cuh).  Shared by the shared-memory wavefront and pt_trace_primary so that the
+// parity hook runs exactly the scan the render runs.
+inline int pick_scan_mode(const SceneDev& scene, const pt_camera& cam, uint32_t traversal) {
+    const bool param_ok = scene.brute && scene.n_pairs > 0 && scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty();
+    if (!param_ok || traversal == PT_TRAVERSAL_BRUTE_TABLE) return 1;
+    bool in_domain = scene.fp32_domain;
+    for (int k = 0; k < 3; ++k) if (!(fabsf(cam.origin[k]) <= kFp32DomainMax)) in_domain = false;
+    return (in_domain && traversal != PT_TRAVERSAL_BRUTE_PARAM_CHECKED) ? 3 : 2;
+}
+inline BruteParam make_brute_param(const SceneDev& scene) {   // right-aligned: the scan is entered at slot kParamPairs - n_pairs (PT_PARAM_SCAN)
+    BruteParam bp;
+    memset(&bp, 0, sizeof(bp));
+    if (scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty())
+        memcpy(bp.e + 5 * ((size_t)kParamPairs - scene.n_pairs), scene.brute_host.data(), sizeof(float4) * 5 * (size_t)scene.n_pairs);
+    return bp;
 }
 inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {
     Frame f;

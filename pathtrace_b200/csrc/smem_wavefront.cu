@@ -27,7 +27,6 @@
 // CTAs never communicate, so one launch renders the frame: no per-bounce launches, no host round trips.
 #include <cmath>
 #include <cstdio>
-#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -214,12 +213,12 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                 VertexOut vo = shade_vertex(sc, f, mis, s_ro[j], s_rd[j], v3(s_beta[j]), s_hit[j], meta);
                 finished = vo.finished;
                 c_vertex += vo.vertex ? 1u : 0u;
+                p_hit = v3(vo.new_ro);                                // a finished path may still owe its last vertex's shadow ray
+                emit_shadow = vo.emit_shadow; sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
                 if (vo.finished) {
                     // K8 accumulate (world.rs:296-313)
                     if (vo.add_L) atomicAdd(f.accum + META_PIXEL(meta), make_float4(vo.Ladd.x, vo.Ladd.y, vo.Ladd.z, 0.f));
                 } else {
-                    p_hit = v3(vo.new_ro);
-                    emit_shadow = vo.emit_shadow; sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
                     s_ro[j] = vo.new_ro; s_rd[j] = vo.new_rd; s_meta[j] = vo.new_meta;
                     s_beta[j] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
                     ++c_scatter;
@@ -285,16 +284,8 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kSwBlock, smem));
         return PT_OK;
     };
-    // brute force over a table whose pairs all fit the kernel parameter: MODE 2 (env PT_SW_NO_PARAM=1 keeps MODE 1, for A/B runs)
-    static const bool no_param = getenv("PT_SW_NO_PARAM") != nullptr;
-    static const bool checked = getenv("PT_SW_CHECKED") != nullptr;   // A/B runs: keep MODE 2 where MODE 3 applies
-    auto in_domain = [](const float* v) { for (int k = 0; k < 3; ++k) if (!(fabsf(v[k]) <= kFp32DomainMax)) return false; return true; };
-    const bool unchecked = scene.fp32_domain && in_domain(rl.cam.origin) && !checked;
-    const int mode = !brute ? 0 : (scene.brute && scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty() && !no_param) ? (unchecked ? 3 : 2) : 1;
-    BruteParam bp;
-    memset(&bp, 0, sizeof(bp));
-    if (mode >= 2)   // right-aligned: the scan is entered at slot kParamPairs - n_pairs (pt_wave.cuh: PT_PARAM_SCAN)
-        memcpy(bp.e + 5 * ((size_t)kParamPairs - scene.n_pairs), scene.brute_host.data(), sizeof(float4) * 5 * (size_t)scene.n_pairs);
+    const int mode = !brute ? 0 : pick_scan_mode(scene, rl.cam, rl.prm.traversal);
+    const BruteParam bp = make_brute_param(scene);
     int occ = 0, rc;
     auto with_kernel = [&](auto&& fn) -> int {
         switch (mode * 2 + (profile ? 1 : 0)) {
@@ -355,6 +346,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         stats->rays_primary = a; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
         stats->wavefront_iters = itmax; stats->kernel_launches = 1; stats->path_pool = grid * kSwSlots;
         stats->n_kernel[PT_K_SMEM_WAVEFRONT] = 1;
+        stats->scan_mode = (uint32_t)mode;
         if (profile) {
             float ms = 0;
             cudaEventElapsedTime(&ms, ctx->prof_events[0], ctx->prof_events[1]);

@@ -16,8 +16,6 @@
 #include <cstdio>
 #include <vector>
 
-#include <cstdlib>
-
 #include "pt_wave.cuh"
 
 using namespace ptw;
@@ -45,7 +43,8 @@ static_assert(PT_SHADE_SLOTS % 64 == 0, "a chunk must lie inside one shadow-queu
 // device counter block (uint64 words)
 // device counter block (uint64 words); every counter sits in its own 256-byte line so their L2 atomics do not serialise
 enum { C_STRIDE = 32, C_WORK_NEXT = 0, C_SHADOW_BASE = C_STRIDE, C_ALIVE_BASE = C_SHADOW_BASE + kItersPerBatch * C_STRIDE,
-       C_TOTAL = C_ALIVE_BASE + kItersPerBatch * C_STRIDE };
+       C_WALK = C_ALIVE_BASE + kItersPerBatch * C_STRIDE,   // PT_FLAG_COUNTERS: [0] LBVH node fetches, [1] primitive tests
+       C_TOTAL = C_WALK + C_STRIDE };
 
 struct Pool {
     uint32_t P;
@@ -128,8 +127,9 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
 #ifndef PT_STREAM_MINB
 #define PT_STREAM_MINB 5   // resident CTAs per SM asked of the L1/L2 walk
 #endif
-template <bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t chunk, unsigned long long* __restrict__ next_chunk) {
+template <bool SMEM, bool COUNT>
+__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t chunk, unsigned long long* __restrict__ next_chunk,
+                                                                                            unsigned long long* __restrict__ walk_counters) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
     const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
@@ -155,11 +155,11 @@ __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_clo
         return got;
     };
     auto finish = [&](uint32_t slot, float t, int id) { pool.hit[slot] = make_uint2(__float_as_uint(t), (uint32_t)id); };
-    bvh_stream<SMEM, false>(g, t_min, next, finish);
+    bvh_stream<SMEM, false, COUNT>(g, t_min, next, finish, walk_counters);
 }
-template <bool SMEM>
+template <bool SMEM, bool COUNT>
 __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t chunk,
-                                                                                           unsigned long long* __restrict__ next_chunk) {
+                                                                                           unsigned long long* __restrict__ next_chunk, unsigned long long* __restrict__ walk_counters) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
     const uint32_t lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_sha
             atomicAdd(accum + __float_as_uint(pool.sh_d[slot].w), make_float4(c.x, c.y, c.z, 0.f));
         }
     };
-    bvh_stream<SMEM, true>(g, t_min, next, finish);
+    bvh_stream<SMEM, true, COUNT>(g, t_min, next, finish, walk_counters);
 }
 
 // ------------------------------------------------------------------------------------ shade
@@ -336,9 +336,9 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool poo
                 VertexOut vo = shade_vertex(sg, f, mis, ro4, rd4, beta, h, meta);
                 finished = vo.finished; add_L = vo.add_L; Ladd = vo.Ladd;
                 c_vertex += vo.vertex ? 1u : 0u;
+                emit_shadow = vo.emit_shadow;                         // a finished path may still owe its last vertex's shadow ray
+                sh_o = v3(vo.new_ro); sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
                 if (!vo.finished) {
-                    emit_shadow = vo.emit_shadow;
-                    sh_o = v3(vo.new_ro); sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
                     pool.beta[i] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
                     pool.ray_o[i] = vo.new_ro;
                     pool.ray_d[i] = vo.new_rd;
@@ -400,20 +400,22 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool poo
     }
 }
 
-// K8 — world.rs:315-332: mean, store linear radiance, sqrt gamma, clamp [0,1], *255 truncated, alpha 255
-__global__ void k_resolve(const float4* __restrict__ accum, uint32_t npix, float inv_spp, float* __restrict__ radiance,
+// K8 — world.rs:315-332: mean, store linear radiance, sqrt gamma, clamp [0,1], *255 truncated, alpha 255.
+// The mean is the correctly rounded FP32 quotient; gamma runs in f64 on that value exactly as world.rs:321-332 does on its f64
+// mean, so the bytes equal the reference's tone map of the same radiance (tests/test_gpu_outputs.py) whatever -prec-sqrt says.
+__global__ void k_resolve(const float4* __restrict__ accum, uint32_t npix, float spp, float* __restrict__ radiance,
                           uchar4* __restrict__ rgba) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npix) return;
     float4 a = accum[i];
-    float r = a.x * inv_spp, g = a.y * inv_spp, b = a.z * inv_spp;
+    float r = __fdiv_rn(a.x, spp), g = __fdiv_rn(a.y, spp), b = __fdiv_rn(a.z, spp);
     if (radiance) { radiance[3 * (size_t)i] = r; radiance[3 * (size_t)i + 1] = g; radiance[3 * (size_t)i + 2] = b; }
     if (rgba) {
         auto to8 = [](float v) -> unsigned char {
-            float s = sqrtf(v);
+            double s = __dsqrt_rn((double)v);
             if (!(s == s)) return 0;   // Rust: NaN as u8 == 0
-            s = fminf(fmaxf(s, 0.0f), 1.0f);
-            return (unsigned char)(s * 255.0f);
+            s = s < 0.0 ? 0.0 : (s > 1.0 ? 1.0 : s);
+            return (unsigned char)(s * 255.0);
         };
         rgba[i] = make_uchar4(to8(r), to8(g), to8(b), 255);
     }
@@ -441,10 +443,52 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary(SceneView s, const __g
     if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
 }
 
+// The same hook through the constant-bank scan of the shared-memory wavefront (closest_hit_param, MODE 2 / 3 there).
+template <bool CHECKED>
+__global__ void __launch_bounds__(kBlock) k_trace_primary_param(SceneView s, const __grid_constant__ Frame f, int jitter, float ox, float oy, uint32_t sample,
+                                                                int32_t* __restrict__ obj, float* __restrict__ tt, float* __restrict__ dirs,
+                                                                const __grid_constant__ BruteParam bp) {
+    extern __shared__ float4 smem[];
+    Geo<true> g = stage_scene<true>(s, smem, false);
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.npix) return;
+    uint32_t x = i % f.cam.width, y = i / f.cam.width;
+    if (jitter) {
+        uint4 r = philox4x32_10(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+        ox = u01(r.x); oy = u01(r.y);
+    }
+    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
+    float t; int id;
+    closest_hit_param<CHECKED>(bp, g, f.cam.origin, d, f.t_min, t, id);
+    obj[i] = id;
+    tt[i] = id >= 0 ? t : __int_as_float(0x7f800000);
+    if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
+}
+
+// pt_render_moments: total += batch, moment2 += batch^2, batch = 0
+__global__ void k_fold_moments(float4* __restrict__ batch, float4* __restrict__ total, float4* __restrict__ m2, uint32_t npix) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    const float4 b = batch[i];
+    float4 t = total[i], q = m2[i];
+    t.x += b.x; t.y += b.y; t.z += b.z;
+    q.x = fmaf(b.x, b.x, q.x); q.y = fmaf(b.y, b.y, q.y); q.z = fmaf(b.z, b.z, q.z);
+    total[i] = t; m2[i] = q;
+    batch[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__global__ void k_moments_out(const float4* __restrict__ m2, uint32_t npix, float* __restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix) return;
+    const float4 q = m2[i];
+    out[3 * (size_t)i] = q.x; out[3 * (size_t)i + 1] = q.y; out[3 * (size_t)i + 2] = q.z;
+}
+
 struct Mode { bool smem, brute; size_t smem_bytes; };
 Mode pick_mode(const SceneDev& s, uint32_t traversal) {
     Mode m;
-    m.brute = traversal == PT_TRAVERSAL_BRUTE || (traversal == PT_TRAVERSAL_AUTO && s.n_objects <= 16);
+    // A tree over fewer than two objects has no inner node to walk (lbvh.cu: k_trivial_tree exists for pt_bvh_download only):
+    // such scenes are always scanned.
+    m.brute = traversal >= PT_TRAVERSAL_BRUTE || (traversal == PT_TRAVERSAL_AUTO && s.n_objects <= 16) || s.n_objects < 2;
     m.smem = s.n_objects <= kMaxSmemPrims;
     m.smem_bytes = !m.smem ? 0 : (m.brute && s.brute) ? sizeof(float4) * 5 * (size_t)s.n_brute
                                                      : sizeof(float4) * ((m.brute ? 0 : (size_t)s.n_nodes * 4) + (size_t)s.n_objects * 3);
@@ -500,7 +544,18 @@ int fp32_peak_launch(pt_context* ctx, float* tflops, float* ms_out) {
 
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba) {
     uint32_t npix = w * h;
-    k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_accum, npix, 1.0f / (float)spp, d_rad, reinterpret_cast<uchar4*>(d_rgba));
+    k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_accum, npix, (float)spp, d_rad, reinterpret_cast<uchar4*>(d_rgba));
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    return PT_OK;
+}
+
+int fold_moments_launch(pt_context* ctx, float4* d_batch, float4* d_total, float4* d_moment2, uint32_t npix) {
+    k_fold_moments<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_batch, d_total, d_moment2, npix);
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    return PT_OK;
+}
+int moments_out_launch(pt_context* ctx, const float4* d_moment2, uint32_t npix, float* d_out_rgb) {
+    k_moments_out<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_moment2, npix, d_out_rgb);
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     return PT_OK;
 }
@@ -511,6 +566,20 @@ int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_cam
     Frame f = make_frame(cam, prm, nullptr);
     Mode mode = pick_mode(scene, prm.traversal);
     uint32_t grid = (f.npix + kBlock - 1) / kBlock;
+    const int scan = (mode.brute && mode.smem && scene.brute) ? pick_scan_mode(scene, cam, prm.traversal) : 0;
+    if (scan >= 2) {   // the constant-bank scan the shared-memory wavefront runs on this scene
+        const BruteParam bp = make_brute_param(scene);
+        if (scan == 2) {
+            int rc = set_smem(ctx, k_trace_primary_param<true>, mode.smem_bytes); if (rc) return rc;
+            k_trace_primary_param<true><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp);
+        } else {
+            int rc = set_smem(ctx, k_trace_primary_param<false>, mode.smem_bytes); if (rc) return rc;
+            k_trace_primary_param<false><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp);
+        }
+        PT_CUDA_CHECK(ctx, cudaGetLastError());
+        if (launches) *launches += 1;
+        return PT_OK;
+    }
 #define CALL(S, B)                                                                                                            \
     {                                                                                                                         \
         int rc = set_smem(ctx, k_trace_primary<S, B>, mode.smem_bytes);                                                       \
@@ -575,27 +644,28 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #define SETS(S, B) { rc = set_smem(ctx, k_trace_closest<S, B>, mode.smem_bytes); if (rc) return rc; rc = set_smem(ctx, k_trace_shadow<S, B>, mode.smem_bytes); if (rc) return rc; }
     PT_DISPATCH(mode, SETS);
 #undef SETS
-    // LBVH scenes: a resident grid of warps streams the queues (k_trace_*_stream); env PT_NO_STREAM_BVH=1 keeps one thread
-    // per slot (A/B runs)
-    static const bool no_stream = getenv("PT_NO_STREAM_BVH") != nullptr;
-    const bool stream_bvh = !mode.brute && scene.n_objects >= 2 && !no_stream;
+    // LBVH scenes: a resident grid of warps streams the queues (k_trace_*_stream)
+    const bool stream_bvh = !mode.brute;
+    const bool count = stream_bvh && (rl.prm.flags & PT_FLAG_COUNTERS) != 0;
     uint32_t stream_grid = 0, stream_chunk = 0;
     if (stream_bvh) {
         int occ_c = 0, occ_s = 0;
-        if (mode.smem) {
-            rc = set_smem(ctx, k_trace_closest_stream<true>, mode.smem_bytes); if (rc) return rc;
-            rc = set_smem(ctx, k_trace_shadow_stream<true>, mode.smem_bytes); if (rc) return rc;
-            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_trace_closest_stream<true>, kBlock, mode.smem_bytes));
-            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, k_trace_shadow_stream<true>, kBlock, mode.smem_bytes));
-        } else {
-            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, k_trace_closest_stream<false>, kBlock, 0));
-            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, k_trace_shadow_stream<false>, kBlock, 0));
-        }
+        auto setup = [&](auto kc, auto ks, size_t bytes) -> int {
+            int rc2 = set_smem(ctx, kc, bytes); if (rc2) return rc2;
+            rc2 = set_smem(ctx, ks, bytes); if (rc2) return rc2;
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, kc, kBlock, bytes));
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, ks, kBlock, bytes));
+            return PT_OK;
+        };
+        if (mode.smem) rc = count ? setup(k_trace_closest_stream<true, true>, k_trace_shadow_stream<true, true>, mode.smem_bytes)
+                                  : setup(k_trace_closest_stream<true, false>, k_trace_shadow_stream<true, false>, mode.smem_bytes);
+        else rc = count ? setup(k_trace_closest_stream<false, true>, k_trace_shadow_stream<false, true>, 0)
+                        : setup(k_trace_closest_stream<false, false>, k_trace_shadow_stream<false, false>, 0);
+        if (rc) return rc;
         const int occ = occ_c < occ_s ? occ_c : occ_s;
         if (occ < 1) { ctx->err = "stream traversal kernels do not fit on an SM"; return PT_ERR_CUDA; }
         stream_grid = (uint32_t)ctx->sm_count * (uint32_t)occ;        // one resident wave; the queue is handed out dynamically
-        static const uint32_t env_chunk = getenv("PT_STREAM_CHUNK") ? (uint32_t)atoi(getenv("PT_STREAM_CHUNK")) : 0u;   // tuning runs
-        stream_chunk = env_chunk ? env_chunk : mode.smem ? kStreamChunkSmem : kStreamChunkL2;
+        stream_chunk = mode.smem ? kStreamChunkSmem : kStreamChunkL2;
     }
     const uint32_t sgrid = P / kShadeSlots;
     f.chunk = (f.total_work + sgrid - 1) / sgrid;
@@ -621,6 +691,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     prof_end();
     const bool mis = rl.prm.strategy == PT_STRATEGY_MIS && scene.n_lights > 0;
     bool done = false;
+    uint64_t nodes_visited = 0, prim_tests = 0;
+    unsigned long long* walk = reinterpret_cast<unsigned long long*>(ctx->d_counters + C_WALK);
     while (!done) {
         PT_CUDA_CHECK(ctx, cudaMemsetAsync(ctx->d_counters + C_SHADOW_BASE, 0, 8 * (C_TOTAL - C_SHADOW_BASE), st));
         for (int it = 0; it < kItersPerBatch; ++it) {
@@ -630,8 +702,10 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
             prof_begin(PT_K_TRACE_CLOSEST);
             if (stream_bvh) {
-                if (mode.smem) k_trace_closest_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c);
-                else k_trace_closest_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, stream_chunk, cur_c);
+                if (mode.smem && count) k_trace_closest_stream<true, true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
+                else if (mode.smem) k_trace_closest_stream<true, false><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
+                else if (count) k_trace_closest_stream<false, true><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
+                else k_trace_closest_stream<false, false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
             } else PT_DISPATCH(mode, TRACE);
             prof_end();
 #undef TRACE
@@ -643,8 +717,10 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
                 prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
                 if (stream_bvh) {
-                    if (mode.smem) k_trace_shadow_stream<true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s);
-                    else k_trace_shadow_stream<false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s);
+                    if (mode.smem && count) k_trace_shadow_stream<true, true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else if (mode.smem) k_trace_shadow_stream<true, false><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else if (count) k_trace_shadow_stream<false, true><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else k_trace_shadow_stream<false, false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
                 } else PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
                 prof_end();
@@ -656,6 +732,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
         prof_collect();
         done = ctx->h_counters[C_ALIVE_BASE + (kItersPerBatch - 1) * C_STRIDE] == 0;
+        nodes_visited += ctx->h_counters[C_WALK]; prim_tests += ctx->h_counters[C_WALK + 1];
     }
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     if (stats) {
@@ -666,6 +743,7 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
         stats->samples = f.total_work;
         stats->rays_primary = a; stats->rays_shadow = b; stats->rays_scattered = c; stats->path_vertices = d;
         stats->wavefront_iters = iters; stats->kernel_launches = launches; stats->path_pool = P;
+        stats->nodes_visited = nodes_visited; stats->prim_tests = prim_tests; stats->scan_mode = 0xffffffffu;
         for (int k = 0; k < PT_K_COUNT; ++k) { stats->ms_kernel[k] = ms_k[k]; stats->n_kernel[k] = n_k[k]; }
     }
     return PT_OK;

@@ -41,15 +41,18 @@ def render_distributed(ctx, scene, cam, spp: int, *, rank: int, world: int, para
     dev = torch.device("cuda", ctx.device)
     stream = torch.cuda.ExternalStream(ctx.stream, device=dev)
     spp_g, off_g = split_spp(spp, world, rank)
-    accum = torch.zeros(W * H, 4, device=dev, dtype=torch.float32)
     stats = None
+    # the library's stream is non-blocking (no implicit ordering against torch's default stream): allocate and clear the sum
+    # buffer on the stream that renders into it
     with torch.cuda.stream(stream):
+        accum = torch.empty(W * H, 4, device=dev, dtype=torch.float32)
         accum.zero_()
         if spp_g > 0:
             p = api.render_params(spp=spp_g, sample_offset=off_g, **(params_kw or {}))
             stats = api.render_accumulate_device(ctx, scene, cam, p, accum.data_ptr())
         reduce_sum(accum, 0, group)
         if rank != 0:
+            stream.synchronize()          # accum is released on return: the reduce must have consumed it
             return None, None, stats
         radiance = torch.empty(W * H, 3, device=dev, dtype=torch.float32)
         rgba = torch.empty(W * H, 4, device=dev, dtype=torch.uint8)
