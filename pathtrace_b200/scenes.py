@@ -1,6 +1,7 @@
 """Scene builders: the reference's default scene and the synthetic benchmark scenes of BASELINE.json.
 
 default_scene()      — World::new's 13-object Cornell box, src/world.rs:65-241
+material_zoo()       — the same box with every material model and both light shapes the object API can build (parity scene)
 random_spheres()     — config C3 (~500 spheres, mixed diffuse/metal/dielectric), SURVEY §8(d)
 heightfield()        — config C4 (1,002,528 triangles + emissive quad), SURVEY §8(d)
 Each returns (objects-or-arrays, Camera factory); all go through the object API of objects.py.
@@ -10,7 +11,7 @@ from __future__ import annotations
 import numpy as np
 
 from .objects import (MATERIAL_DTYPE, PT_MAT_EMISSIVE, PT_MAT_LAMBERTIAN, PT_SHAPE_TRIANGLE, SHAPE_DTYPE, Camera, Emissive,
-                      LambertianCosineWeighted, Mirror, Object, SphereShape, TriangleShape, Vector3, describe_objects)
+                      LambertianCosineWeighted, Mirror, Object, OrenNayar, SphereShape, TriangleShape, Vector3, describe_objects)
 
 V = Vector3.new
 
@@ -50,6 +51,43 @@ def default_camera(width=WIDTH, height=HEIGHT):
 
 def default_scene(width=WIDTH, height=HEIGHT):
     shapes, mats = describe_objects(default_objects())
+    return shapes, mats, default_camera(width, height)
+
+
+def material_zoo_objects():
+    """A 16-object parity scene that puts every constructible material and both light shapes in front of the oracle:
+    Lambertian walls (material.rs:67-123), Oren-Nayar floor (sigma 0.8) and back wall (sigma 0.2) (material.rs:166-296),
+    a metallic GGX sphere with coloured F0 (mirror.rs:126-132, metallic > 0.99 branch :187/:227), a rough-glass sphere
+    (metallic 0), a rough metallic triangle, a two-triangle light and a SPHERE light (shape.rs:91-145) — the commented-out
+    variants of world.rs:183-200 made live.  Object order = object id."""
+    bs, bd, ls = 1.0, -2.0, 0.3
+    tri = lambda a, b, c, m: Object.new(TriangleShape.new(V(*a), V(*b), V(*c)), m)
+    red = LambertianCosineWeighted.new(V(0.8, 0.1, 0.1)); green = LambertianCosineWeighted.new(V(0.1, 0.8, 0.1))
+    back = OrenNayar.new(V(0.3, 0.3, 0.8), 0.2); floor = OrenNayar.new(V(0.7, 0.7, 0.6), 0.8)
+    ceil = LambertianCosineWeighted.new(V(0.8, 0.8, 0.8)); light = Emissive.new(V(12.0, 12.0, 12.0))
+    zb, zf, ly = bd - bs, bd + bs, bs - 0.01
+    return [
+        tri((-bs, -bs, zb), (-bs, bs, zb), (-bs, bs, zf), red),        # 0 left wall
+        tri((-bs, -bs, zb), (-bs, bs, zf), (-bs, -bs, zf), red),       # 1
+        tri((bs, -bs, zb), (bs, bs, zf), (bs, bs, zb), green),         # 2 right wall
+        tri((bs, -bs, zb), (bs, -bs, zf), (bs, bs, zf), green),        # 3
+        tri((-bs, -bs, zb), (bs, -bs, zb), (bs, bs, zb), back),        # 4 back wall, Oren-Nayar 0.2
+        tri((-bs, -bs, zb), (bs, bs, zb), (-bs, bs, zb), back),        # 5
+        tri((-bs, -bs, zb), (bs, -bs, zf), (bs, -bs, zb), floor),      # 6 floor, Oren-Nayar 0.8
+        tri((-bs, -bs, zb), (-bs, -bs, zf), (bs, -bs, zf), floor),     # 7
+        tri((-bs, bs, zb), (bs, bs, zb), (bs, bs, zf), ceil),          # 8 ceiling
+        tri((-bs, bs, zb), (bs, bs, zf), (-bs, bs, zf), ceil),         # 9
+        tri((0.1, ly, bd - ls), (0.7, ly, bd - ls), (0.7, ly, bd + ls), light),     # 10 triangle light
+        tri((0.1, ly, bd - ls), (0.7, ly, bd + ls), (0.1, ly, bd + ls), light),     # 11
+        Object.new(SphereShape.new(V(-0.55, 0.35, -2.4), 0.15), Emissive.new(V(20.0, 16.0, 10.0))),                                  # 12 sphere light
+        Object.new(SphereShape.new(V(0.45, -0.6, -1.9), 0.4), Mirror(roughness=0.25, color=V(0.95, 0.64, 0.54), metallic=1.0, ior=1.5)),   # 13 copper
+        Object.new(SphereShape.new(V(-0.45, -0.65, -1.7), 0.35), Mirror(roughness=0.15, color=V(1.0, 1.0, 1.0), metallic=0.0, ior=1.5)),   # 14 glass
+        tri((-0.95, -0.2, -2.9), (-0.2, -0.2, -2.95), (-0.6, 0.7, -2.6), Mirror(roughness=0.5, color=V(0.9, 0.9, 0.3), metallic=1.0, ior=1.5)),  # 15 brass panel
+    ]
+
+
+def material_zoo_scene(width=128, height=128):
+    shapes, mats = describe_objects(material_zoo_objects())
     return shapes, mats, default_camera(width, height)
 
 

@@ -19,6 +19,7 @@ def _scenes():
     out["default"] = (sh, mt, cam)
     sh, mt, cam = scenes.random_spheres_scene(200, 112)
     out["spheres"] = (sh, mt, cam)
+    out["zoo"] = scenes.material_zoo_scene(160, 120)
     for seed, n in ((1, 2), (2, 3), (3, 17), (4, 300), (5, 5000)):
         sh, mt = random_scene(seed, n)
         out[f"random{n}"] = (sh, mt, Camera.new(Vector3.new(0, 0, 2), 96, 64, 1.0, 35.0))
@@ -50,14 +51,19 @@ def test_lbvh_trivial(n, oracle, gpu_ctx):
     assert np.array_equal(got["nodes"], ref["nodes"])
 
 
-@pytest.mark.parametrize("name", ["default", "spheres", "random2", "random17", "random300", "random5000"])
-@pytest.mark.parametrize("traversal", ["bvh", "brute"])
+@pytest.mark.parametrize("name", ["default", "zoo", "spheres", "random2", "random17", "random300", "random5000"])
+@pytest.mark.parametrize("traversal", ["bvh", "brute", "brute_table", "brute_param_checked"])
 @pytest.mark.parametrize("jitter", [False, True])
 def test_primary_hits(name, traversal, jitter, oracle, gpu_ctx):
+    """`brute` is the scan the render (and the benchmark) runs on that scene: for the default scene and the zoo the triangle
+    pairs come from the constant bank with the in-domain pair test (pt_stats.scan_mode 3, closest_hit_param<false>);
+    `brute_param_checked` / `brute_table` are its conservative forms; all must give the FP32 oracle's ids and t bit for bit."""
     from pathtrace_b200 import api
     sh, mt, cam = _scenes()[name]
-    if traversal == "brute" and len(sh) > 1000:
+    if traversal.startswith("brute") and len(sh) > 1000:
         pytest.skip("brute force over 5000 objects is covered by the bvh run")
+    if traversal in ("brute_table", "brute_param_checked") and name not in ("default", "zoo", "random17"):
+        pytest.skip("the forced scan forms are exercised on the scenes whose pairs fit the constant bank")
     ocam = oracle_camera(oracle, cam)
     sc = api.Scene(gpu_ctx, sh, mt)
     ids, t, dirs = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal=traversal), jitter=jitter, sample=3, want_dirs=True)
@@ -75,9 +81,9 @@ def test_primary_hits(name, traversal, jitter, oracle, gpu_ctx):
     # north-star bar: 1e-5 relative.  Held everywhere on the default scene; on sphere-heavy scenes a ray that
     # grazes a sphere's silhouette is ill-conditioned (dt ~ sqrt of the FP32 rounding of the ray direction
     # itself), so there the bar is: >= 99.9 % of pixels within 1e-5 and none beyond 1e-3.
-    if name == "default":
+    if name in ("default", "zoo"):
         assert rel.max() <= 1e-5, rel.max()
-    else:
+    else:   # the conditioning-aware form of the bar is asserted in test_gpu_materials.py::test_hit_distance_bar_on_sphere_scenes
         assert (rel > 1e-5).mean() < 1e-3 and rel.max() < 1e-3, ((rel > 1e-5).mean(), rel.max())
     # id disagreements with f64 only on shared edges: a handful
     assert (did != ids).mean() < 2e-2
@@ -186,3 +192,43 @@ def test_single_samples_match_fp32_oracle(hbm_queues, oracle, gpu_ctx):
     print("pixels agreeing:", agree / total, "energy ratio", sum_g / sum_c)
     assert agree / total > 0.995
     assert abs(sum_g / sum_c - 1.0) < 0.01
+
+
+def test_benchmark_scan_mode_is_the_one_trace_primary_checks(gpu_ctx):
+    """The default scene renders through scan mode 3 (constant-bank pairs, in-domain pair test); `brute_table` and
+    `brute_param_checked` select modes 1 and 2; all three trace the same paths."""
+    from pathtrace_b200 import api, scenes
+    sh, mt, cam = scenes.default_scene(96, 64)
+    sc = api.Scene(gpu_ctx, sh, mt)
+    out = {}
+    for trav, mode in (("auto", 3), ("brute", 3), ("brute_param_checked", 2), ("brute_table", 1), ("bvh", 0)):
+        rad, _, st = api.render(gpu_ctx, sc, cam, api.render_params(spp=8, traversal=trav))
+        assert st["scan_mode"] == mode and st["n_kernel"]["smem_wavefront"] == 1, (trav, st["scan_mode"])
+        out[trav] = (rad, st)
+    sc.close()
+    for trav in ("brute", "brute_param_checked", "brute_table", "bvh"):
+        for k in ("rays_primary", "rays_shadow", "rays_scattered", "path_vertices"):
+            assert out[trav][1][k] == out["auto"][1][k], (trav, k)
+        assert np.allclose(out[trav][0], out["auto"][0], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("n", [0, 1])
+@pytest.mark.parametrize("hbm_queues", [False, True])
+def test_forced_bvh_on_trivial_scenes(n, hbm_queues, oracle, gpu_ctx):
+    """A tree over fewer than two objects has no inner node: PT_TRAVERSAL_BVH must fall back to the scan instead of walking
+    the placeholder node (whose missing child is an out-of-range primitive)."""
+    from pathtrace_b200 import api
+    from pathtrace_b200.objects import Camera, Vector3
+    sh, mt = random_scene(7, n)
+    cam = Camera.new(Vector3.new(0, 0, 2), 48, 32, 1.0, 35.0)
+    sc = api.Scene(gpu_ctx, sh, mt)
+    ids, t, _ = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal="bvh"))
+    rid, rt, _ = oracle.trace_primary(oracle_camera(oracle, cam), sh, mt, precision="f32")
+    assert np.array_equal(ids, rid)
+    hit = rid >= 0
+    assert np.array_equal(t[hit].view(np.uint32), rt[hit].astype(np.float32).view(np.uint32))
+    rad, _, st = api.render(gpu_ctx, sc, cam, api.render_params(spp=4, traversal="bvh", hbm_queues=hbm_queues))
+    sc.close()
+    assert np.isfinite(rad).all() and st["rays_primary"] == 4 * 48 * 32
+    if n == 0:
+        assert not rad.any()

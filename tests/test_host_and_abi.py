@@ -94,3 +94,55 @@ def test_splitmix_vector_twin():
     r = SplitMix64(0x5EED0004)
     a = np.array([r.uniform() for _ in range(100)])
     assert np.array_equal(a, splitmix64_array(0x5EED0004, 100))
+
+
+def test_luminance_csv_writer_equals_oracle_bytes(tmp_path, oracle):
+    """world.rs:344-369.  pt_export_luminance is host code (no device needed): its file equals the oracle's byte for byte,
+    Rust's NaN / inf / -inf spellings included."""
+    from pathtrace_b200 import api
+    rng = np.random.default_rng(5)
+    rad = rng.uniform(0, 3, (7, 5, 3)).astype(np.float32)
+    rad[0, 0] = [np.nan, np.inf, -np.inf]
+    rad[1, 2] = [-0.0, 1e-7, 123456.789]
+    rad[2, 2] = [0.0000005, 0.0000015, 2.5]             # exact-decimal rounding of the f32 values promoted to f64
+    a, b = os.path.join(tmp_path, "lib.csv"), os.path.join(tmp_path, "oracle.csv")
+    api.export_luminance(a, rad)
+    oracle.export_luminance(b, rad.astype(np.float64))
+    assert open(a, "rb").read() == open(b, "rb").read()
+    lines = open(a).read().splitlines()
+    assert lines[0] == "x,y,r,g,b,luminance" and lines[1] == "0,0,NaN,inf,-inf,NaN" and len(lines) == 36
+
+
+def test_header_structs_match_ctypes_mirror():
+    """Field order, offsets and sizes of every struct in include/pathtrace_b200.h against the ctypes mirror in api.py, computed
+    from the header text with the C layout rules (natural alignment)."""
+    from pathtrace_b200 import api
+    header = open(os.path.join(ROOT, "include", "pathtrace_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    sizes = {"uint32_t": 4, "int32_t": 4, "uint64_t": 8, "float": 4, "uint8_t": 1}
+
+    def layout(name):
+        body = re.search(r"typedef struct \{([^{}]*)\}\s*" + name + r"\s*;", header).group(1)
+        fields, off, align = [], 0, 1
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            ty, rest = decl.split(None, 1)
+            for item in rest.split(","):
+                m = re.match(r"\s*(\w+)(?:\[(\d+)\])?\s*$", item)
+                n = int(m.group(2) or 1)
+                sz = sizes[ty]
+                off = (off + sz - 1) // sz * sz
+                fields.append((m.group(1), off, sz * n))
+                off += sz * n
+                align = max(align, sz)
+        return fields, (off + align - 1) // align * align
+
+    for name, mirror in (("pt_camera", api.pt_camera), ("pt_render_params", api.pt_render_params), ("pt_stats", api.pt_stats)):
+        fields, size = layout(name)
+        assert size == ctypes.sizeof(mirror), (name, size, ctypes.sizeof(mirror))
+        assert [f[0] for f in fields] == [f[0] for f in mirror._fields_], name
+        for fname, off, sz in fields:
+            d = getattr(mirror, fname)
+            assert (d.offset, d.size) == (off, sz), (name, fname, off, sz, d.offset, d.size)
