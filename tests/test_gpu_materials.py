@@ -74,7 +74,10 @@ def test_single_samples_match_fp32_oracle_all_materials(scene_name, mode, strate
         sum_g += float(rad.sum()); sum_c += float(c.sum())
         npx = cam.width * cam.height
         assert st["rays_primary"] == npx
-        assert abs(st["path_vertices"] - r["counters"]["vertices"]) <= 0.01 * npx
+        # The oracle walks a path whose GGX sample failed (the reference's (normal, 0, 1, 0) tuple, mirror.rs:258-265) on with zero
+        # throughput until roulette kills it; the device ends it at once (same radiance): it shades a few vertices less.
+        dv = r["counters"]["vertices"] - st["path_vertices"]
+        assert -0.01 * npx <= dv <= 0.04 * npx, dv
         if strategy == "brdf_only":
             assert st["rays_shadow"] == 0                                  # no NEE in BrdfOnlyStrategy
     sc.close()
@@ -157,7 +160,7 @@ def test_hit_distance_bar_on_sphere_scenes(oracle, gpu_ctx):
     sc.close()
     did, dt, _ = oracle.trace_primary(ocam, sh, mt, precision="f64")
     same = (did == ids) & (ids >= 0)
-    assert same.mean() > 0.95 and (did != ids).mean() < 5e-3
+    assert same.sum() > 0.99 * (ids >= 0).sum() and (ids >= 0).mean() > 0.5 and (did != ids).mean() < 5e-3
     rel = np.abs(t.astype(np.float64) - dt) / np.where(same, dt, 1.0)
     o = np.array([cam.origin.x, cam.origin.y, cam.origin.z])
     p = o + dirs.astype(np.float64) * dt[..., None]
