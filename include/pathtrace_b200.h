@@ -49,16 +49,21 @@ typedef struct {
 /* Compile-time constants / cargo features of the reference turned into run-time fields:
  * SAMPLE_NUM world.rs:18; MIN_DEPTH/MAX_DEPTH/NUM_LIGHT_SAMPLES rendering.rs:6-10; features mis|brdf_only Cargo.toml:6-10. */
 enum { PT_STRATEGY_MIS = 0, PT_STRATEGY_BRDF_ONLY = 1 };
-/* How hit_scene (world.rs:270-290) is evaluated.  Every value returns the same closest hit (id and t bit-equal, tie rule
- * included).
+/* How hit_scene (world.rs:270-290) is evaluated.  PRIMARY rays get the same closest hit from every value except BRUTE_FAST (id
+ * and t bit-equal to the FP32 restatement of shape.rs, tie rule included).
  *   AUTO        <= 16 objects: BRUTE; more: BVH
- *   BVH         GPU-built LBVH
- *   BRUTE       linear scan in object order like the reference; the library picks the fastest bit-exact form the scene allows
- *               (triangle pairs from the constant bank, unchecked reciprocal inside the FP32 coordinate domain)
- *   BRUTE_TABLE the scan table from shared memory with every range check (the conservative form of BRUTE)
- *   BRUTE_PARAM_CHECKED  the constant-bank scan with every range check */
+ *   BVH         GPU-built LBVH (exact primitive tests for every ray)
+ *   BRUTE       linear scan in object order like the reference.  The library picks the fastest form the scene allows: triangle
+ *               pairs from the constant bank, unchecked reciprocal inside the FP32 coordinate domain, and — for shadow and
+ *               scattered rays, which the parity contract holds to 1e-5 on t rather than to the bit — a precomputed-transform
+ *               test per triangle or parallelogram (pt_stats.scan_mode 4)
+ *   BRUTE_EXACT as BRUTE with the bit-exact Moller-Trumbore test for every ray (scan_mode 3)
+ *   BRUTE_PARAM_CHECKED  as BRUTE_EXACT with every range check (scan_mode 2)
+ *   BRUTE_TABLE the scan table from shared memory with every range check (scan_mode 1)
+ *   BRUTE_FAST  parity hook: the secondary-ray test applied to every ray, so that pt_trace_primary can put it in front of the
+ *               oracle (ids equal except on shared edges, t within 1e-5) */
 enum { PT_TRAVERSAL_AUTO = 0, PT_TRAVERSAL_BVH = 1, PT_TRAVERSAL_BRUTE = 2, PT_TRAVERSAL_BRUTE_TABLE = 3, PT_TRAVERSAL_BRUTE_PARAM_CHECKED = 4,
-       PT_TRAVERSAL_COUNT = 5 };
+       PT_TRAVERSAL_BRUTE_EXACT = 5, PT_TRAVERSAL_BRUTE_FAST = 6, PT_TRAVERSAL_COUNT = 7 };
 typedef struct {
     uint32_t spp;              /* samples per pixel rendered by THIS call */
     uint32_t sample_offset;    /* global index of the first sample (spp split across GPUs / progressive chunks); offset + spp <= 2^24 */
@@ -94,7 +99,8 @@ typedef struct {
     uint32_t n_kernel[5];       /* launches per kernel class */
     uint32_t path_pool;         /* pool size actually used */
     float phase_share[3];       /* PT_FLAG_PROFILE, shared-memory wavefront: share of warp cycles in closest-hit items, shading (+ shadow ray) items, waiting */
-    uint32_t scan_mode;         /* shared-memory wavefront: 0 LBVH, 1 scan table, 2 constant-bank scan (checked), 3 constant-bank scan (in-domain); 0xffffffff otherwise */
+    uint32_t scan_mode;         /* shared-memory wavefront: 0 LBVH, 1 scan table, 2 constant-bank scan (checked), 3 constant-bank scan (in-domain),
+                                   4 = 3 for primary rays + precomputed-transform test for shadow and scattered rays; 0xffffffff otherwise */
 } pt_stats;
 
 typedef struct pt_context pt_context;

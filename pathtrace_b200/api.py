@@ -53,7 +53,7 @@ KERNEL_CLASSES = ("generate", "trace_closest", "shade", "trace_shadow", "smem_wa
 
 
 STRATEGY = {"mis": 0, "brdf_only": 1}
-TRAVERSAL = {"auto": 0, "bvh": 1, "brute": 2, "brute_table": 3, "brute_param_checked": 4}
+TRAVERSAL = {"auto": 0, "bvh": 1, "brute": 2, "brute_table": 3, "brute_param_checked": 4, "brute_exact": 5, "brute_fast": 6}
 
 # every symbol include/pathtrace_b200.h declares
 EXPORTS = ["pt_context_create", "pt_context_destroy", "pt_last_error", "pt_scene_create", "pt_scene_destroy", "pt_render",

@@ -55,6 +55,86 @@ int ensure_frame(pt_context* ctx, size_t npix) {
     }
     return PT_OK;
 }
+// Planar entries for the secondary-ray scan.  An entry is a parallelogram (two consecutive triangles A = (a, s0, s1) and
+// B = (b, s0, s1) with a + b == s0 + s1) or a single triangle, stored as the rows of the affine map world -> (u, v, w) with
+// P = a + u e_u + v e_v + w n (a precomputed-transform test in the manner of Baldwin & Weber 2016): the ray meets the plane
+// at t = -o'_w / d'_w and hits when (u, v) lies in the unit square (parallelogram) or under u + v <= 1 (triangle).
+void build_fast_table(const pt_shape* shapes, uint32_t n, SceneDev& out) {
+    struct Entry { double m[12]; int id_a, id_b; float lim; };
+    std::vector<Entry> entries;
+    auto make = [](const double a[3], const double eu[3], const double ev[3], Entry& e) {
+        double nn[3] = {eu[1] * ev[2] - eu[2] * ev[1], eu[2] * ev[0] - eu[0] * ev[2], eu[0] * ev[1] - eu[1] * ev[0]};
+        const double len = std::sqrt(nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2]);
+        if (!(len > 0.0) || !std::isfinite(len)) return false;
+        for (double& c : nn) c /= len;
+        // inverse of the matrix with columns (eu, ev, nn): rows are cross products over the determinant
+        const double det = eu[0] * (ev[1] * nn[2] - ev[2] * nn[1]) - eu[1] * (ev[0] * nn[2] - ev[2] * nn[0]) + eu[2] * (ev[0] * nn[1] - ev[1] * nn[0]);
+        if (!(std::fabs(det) > 0.0)) return false;
+        const double r0[3] = {(ev[1] * nn[2] - ev[2] * nn[1]) / det, (ev[2] * nn[0] - ev[0] * nn[2]) / det, (ev[0] * nn[1] - ev[1] * nn[0]) / det};
+        const double r1[3] = {(nn[1] * eu[2] - nn[2] * eu[1]) / det, (nn[2] * eu[0] - nn[0] * eu[2]) / det, (nn[0] * eu[1] - nn[1] * eu[0]) / det};
+        const double r2[3] = {(eu[1] * ev[2] - eu[2] * ev[1]) / det, (eu[2] * ev[0] - eu[0] * ev[2]) / det, (eu[0] * ev[1] - eu[1] * ev[0]) / det};
+        const double* rows[3] = {r0, r1, r2};
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 3; ++c) e.m[4 * r + c] = rows[r][c];
+            e.m[4 * r + 3] = -(rows[r][0] * a[0] + rows[r][1] * a[1] + rows[r][2] * a[2]);
+        }
+        for (double v : e.m) if (!std::isfinite(v) || std::fabs(v) > 1e18) return false;
+        return true;
+    };
+    out.fast_host.clear(); out.n_fast_pairs = 0;
+    bool ok = true;
+    for (uint32_t i = 0; i < n && ok; ++i) {
+        if (shapes[i].kind != PT_SHAPE_TRIANGLE) continue;
+        double A[3][3];
+        for (int v = 0; v < 3; ++v) for (int c = 0; c < 3; ++c) A[v][c] = shapes[i].v[3 * v + c];
+        Entry e;
+        bool quad = false;
+        if (i + 1 < n && shapes[i + 1].kind == PT_SHAPE_TRIANGLE) {
+            double B[3][3];
+            for (int v = 0; v < 3; ++v) for (int c = 0; c < 3; ++c) B[v][c] = shapes[i + 1].v[3 * v + c];
+            int sa[2] = {0, 0}, sb[2] = {0, 0}, ns = 0;
+            for (int va = 0; va < 3; ++va)
+                for (int vb = 0; vb < 3; ++vb)
+                    if (A[va][0] == B[vb][0] && A[va][1] == B[vb][1] && A[va][2] == B[vb][2]) { if (ns < 2) { sa[ns] = va; sb[ns] = vb; } ++ns; }
+            if (ns == 2 && sa[0] != sa[1] && sb[0] != sb[1]) {   // exactly one shared edge: the diagonal
+                const int ia = 3 - sa[0] - sa[1], ib = 3 - sb[0] - sb[1];
+                const double *a = A[ia], *b = B[ib], *s0 = A[sa[0]], *s1 = A[sa[1]];
+                double scale = 0, err = 0;
+                for (int c = 0; c < 3; ++c) { err = std::fmax(err, std::fabs(a[c] + b[c] - s0[c] - s1[c])); scale = std::fmax(scale, std::fmax(std::fabs(s0[c] - a[c]), std::fabs(s1[c] - a[c]))); }
+                if (err <= 1e-6 * scale) {
+                    double eu[3], ev[3];
+                    for (int c = 0; c < 3; ++c) { eu[c] = s0[c] - a[c]; ev[c] = s1[c] - a[c]; }
+                    if (make(a, eu, ev, e)) { e.id_a = (int)i; e.id_b = (int)i + 1; e.lim = 2.0f; quad = true; }
+                }
+            }
+        }
+        if (quad) { entries.push_back(e); ++i; continue; }
+        double eu[3], ev[3];
+        for (int c = 0; c < 3; ++c) { eu[c] = A[1][c] - A[0][c]; ev[c] = A[2][c] - A[0][c]; }
+        if (!make(A[0], eu, ev, e)) {           // degenerate triangle: the exact test rejects it too (|a| < 1e-8); keep an entry that never hits
+            for (double& v : e.m) v = 0.0;
+            e.m[11] = 1.0;
+        }
+        e.id_a = e.id_b = (int)i; e.lim = 1.0f;
+        entries.push_back(e);
+    }
+    if (entries.empty() || entries.size() > 2u * kFastParamPairs) return;
+    if (entries.size() & 1u) { Entry d; for (double& v : d.m) v = 0.0; d.m[11] = 1.0; d.id_a = d.id_b = -1; d.lim = 0.0f; entries.push_back(d); }   // w == 1 everywhere: never hit
+    out.n_fast_pairs = (uint32_t)entries.size() / 2;
+    out.fast_host.resize(8 * (size_t)out.n_fast_pairs);
+    for (uint32_t p = 0; p < out.n_fast_pairs; ++p) {
+        const Entry &x = entries[2 * p], &y = entries[2 * p + 1];
+        float4* E = out.fast_host.data() + 8 * (size_t)p;
+        for (int r = 0; r < 3; ++r) {
+            E[2 * r] = make_float4((float)x.m[4 * r], (float)y.m[4 * r], (float)x.m[4 * r + 1], (float)y.m[4 * r + 1]);
+            E[2 * r + 1] = make_float4((float)x.m[4 * r + 2], (float)y.m[4 * r + 2], (float)x.m[4 * r + 3], (float)y.m[4 * r + 3]);
+        }
+        int ia[4] = {x.id_a, y.id_a, x.id_b, y.id_b};
+        std::memcpy(&E[6], ia, 16);
+        E[7] = make_float4(x.lim, y.lim, 0.f, 0.f);
+    }
+}
+
 extern "C" {
 
 const char* pt_version(void) { return "pathtrace_b200 0.2 (sm_100a)"; }
@@ -140,6 +220,7 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
         }
         sc->dev.n_brute = e; sc->dev.n_pairs = pairs;
     }
+    if (sc->dev.n_brute && sc->dev.fp32_domain) build_fast_table(shapes, n, sc->dev);
     pt_shape* d_shapes = nullptr;
     pt_material* d_mats = nullptr;
     auto cleanup = [&](int rc) { if (d_shapes) cudaFree(d_shapes); if (d_mats) cudaFree(d_mats); if (rc) { pt_scene_destroy(sc); } return keep(ctx, rc); };

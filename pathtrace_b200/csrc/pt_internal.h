@@ -10,6 +10,7 @@
 
 constexpr float kFp32DomainMax = 4294967296.0f;   // 2^32, see SceneDev::fp32_domain
 constexpr int kBruteParamPairs = 8;   // pair entries of the scan table that can travel as a kernel parameter (pt_wave.cuh: BruteParam)
+constexpr int kFastParamPairs = 4;    // pairs of planar entries (parallelograms / triangles) of the secondary-ray scan (pt_wave.cuh: FastParam)
 
 // Scene resident in HBM (replicated per GPU).  All arrays are float4-packed for 128-bit loads.
 struct SceneDev {
@@ -25,6 +26,11 @@ struct SceneDev {
     // from 2^126 — the precondition of the unchecked pair test (pt_math.cuh: prcp_rn<false>, hit_triangle2<false, .>).
     bool fp32_domain = false;
     std::vector<float4> brute_host;      // host copy of the pair entries that fit a kernel parameter (pt_wave.cuh: BruteParam)
+    // Secondary-ray scan (pt_wave.cuh: fast_pair): every triangle of the scene as a planar entry with its world -> (u, v, w)
+    // affine map; two consecutive triangles that form a parallelogram share ONE entry.  8 float4 per pair of entries; empty
+    // when the scene's triangles do not fit kFastParamPairs pairs (the exact scan then serves every ray).
+    std::vector<float4> fast_host;
+    uint32_t n_fast_pairs = 0;
     uint32_t* codes_sorted = nullptr;
     uint32_t* prim_sorted = nullptr;
     float bounds[6] = {0, 0, 0, 0, 0, 0};
@@ -90,6 +96,8 @@ int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t 
 int fold_moments_launch(pt_context* ctx, float4* d_batch, float4* d_total, float4* d_moment2, uint32_t npix);
 int moments_out_launch(pt_context* ctx, const float4* d_moment2, uint32_t npix, float* d_out_rgb);
 int fp32_peak_launch(pt_context* ctx, float* tflops, float* ms);
+// capi.cu (host): the planar-entry table of the secondary-ray scan
+void build_fast_table(const pt_shape* shapes, uint32_t n, SceneDev& out);
 int scene_pack_launch(pt_context* ctx, const pt_shape* d_shapes, const pt_material* d_mats, uint32_t n, SceneDev& out);
 
 #define PT_CUDA_CHECK(ctx, expr)                                                                          \

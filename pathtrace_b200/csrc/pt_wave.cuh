@@ -165,6 +165,96 @@ PT_DEV bool any_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd
     return occluded;
 }
 
+// ---- secondary-ray scan.  The north star pins PRIMARY hits bit for bit (ids) and to 1e-5 (t); shadow rays need a boolean and
+// scattered rays a hit that is right to rounding.  For them every triangle is a planar entry (SceneDev::fast_host) tested with
+// its precomputed world -> (u, v, w) affine map: 18 packed FMAs give origin and direction in the entry's frame for TWO entries
+// at once, t = -o_w / d_w, (u, v) = o_uv + t d_uv, and a parallelogram made of two triangles is ONE entry — a third of the
+// arithmetic of two Moller-Trumbore tests per pair of triangles.  Tested against the f64 oracle through pt_trace_primary
+// (PT_TRAVERSAL_BRUTE_FAST): ids equal except on edges, t within 1e-5.
+constexpr int kFastPairs = kFastParamPairs;
+static_assert(kFastPairs == 4, "PT_FAST_SCAN below is written for 4 slots");
+struct FastParam { float4 e[8 * kFastPairs]; };
+#define PT_FAST_SCAN(n_pairs, STEP)                                                                                           \
+    switch (n_pairs) {                                                                                                        \
+        case 4: STEP(0) [[fallthrough]];                                                                                      \
+        case 3: STEP(1) [[fallthrough]];                                                                                      \
+        case 2: STEP(2) [[fallthrough]];                                                                                      \
+        case 1: STEP(3) [[fallthrough]];                                                                                      \
+        default: break;                                                                                                       \
+    }
+// t of both entries and whether each is hit in [t_min, t_max]; uv = u + v tells the two triangles of a parallelogram apart
+PT_DEV float2 fast_pair(const float4* E, float3 ro, float3 rd, float t_min, float t_max, bool& ok_a, bool& ok_b, float2& uv) {
+    const float2 ox = pk(ro.x), oy = pk(ro.y), oz = pk(ro.z), dx = pk(rd.x), dy = pk(rd.y), dz = pk(rd.z);
+    auto row_o = [&](float4 A, float4 B) { return __ffma2_rn(oz, pk(B.x, B.y), __ffma2_rn(oy, pk(A.z, A.w), __ffma2_rn(ox, pk(A.x, A.y), pk(B.z, B.w)))); };
+    auto row_d = [&](float4 A, float4 B) { return __ffma2_rn(dz, pk(B.x, B.y), __ffma2_rn(dy, pk(A.z, A.w), __fmul2_rn(dx, pk(A.x, A.y)))); };
+    const float2 ow = row_o(E[4], E[5]), dw = row_d(E[4], E[5]);
+    float ia, ib;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ia) : "f"(dw.x));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ib) : "f"(dw.y));
+    const float2 t = __fmul2_rn(pneg(ow), pk(ia, ib));
+    const float2 u = __ffma2_rn(t, row_d(E[0], E[1]), row_o(E[0], E[1]));
+    const float2 v = __ffma2_rn(t, row_d(E[2], E[3]), row_o(E[2], E[3]));
+    uv = __fadd2_rn(u, v);
+    // a ray parallel to the plane gives t = +-inf or NaN: refused by the range test (t_max <= FLT_MAX)
+    ok_a = (fminf(u.x, v.x) >= 0.0f) & (fmaxf(u.x, v.x) <= 1.0f) & (uv.x <= E[7].x) & (t.x >= t_min) & (t.x <= t_max);
+    ok_b = (fminf(u.y, v.y) >= 0.0f) & (fmaxf(u.y, v.y) <= 1.0f) & (uv.y <= E[7].y) & (t.y >= t_min) & (t.y <= t_max);
+    return t;
+}
+// shape.rs:53-89 without the correctly rounded divisions and square root of hit_sphere (same cancellation-free quadratic)
+PT_DEV float hit_sphere_fast(float3 c, float radius, float3 ro, float3 rd, float t_min, float t_max) {
+    const float3 oc = ro - c;
+    const float a = dot(rd, rd), bp = -dot(oc, rd);
+    const float ra = __frcp_rn(a) , k = bp * ra;
+    const float3 l = oc + rd * k;
+    const float disc = radius * radius - dot(l, l);
+    const float cc = dot(oc, oc) - radius * radius;
+    const float q = bp + copysignf(sqrtf(fmaxf(a * disc, 0.0f)), bp);
+    const float r0 = __fdividef(cc, q), r1 = q * ra;
+    const float t_near = bp >= 0.0f ? r0 : r1, t_far = bp >= 0.0f ? r1 : r0;
+    const bool near_ok = !(t_near < t_min || t_max < t_near), far_ok = !(t_far < t_min || t_max < t_far);
+    return (disc < 0.0f || !(near_ok || far_ok)) ? -1.0f : (near_ok ? t_near : t_far);
+}
+template <class G>
+PT_DEV void closest_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, const G& g, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
+    best_t = FLT_MAX; best_id = -1;
+    float tmax = FLT_MAX;
+#define PT_STEP(k)                                                                                                            \
+    {                                                                                                                         \
+        bool oka, okb; float2 uv;                                                                                             \
+        const float2 t = fast_pair(fp.e + 8 * (k), ro, rd, t_min, tmax, oka, okb, uv);                                        \
+        const float4 ids = fp.e[8 * (k) + 6];                                                                                 \
+        if (oka) { tmax = t.x; best_id = __float_as_int(uv.x <= 1.0f ? ids.x : ids.z); }                                      \
+        if (okb & (t.y <= tmax)) { tmax = t.y; best_id = __float_as_int(uv.y <= 1.0f ? ids.y : ids.w); }                      \
+    }
+    PT_FAST_SCAN(n_fast_pairs, PT_STEP)
+#undef PT_STEP
+    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e) {            // the unpaired primitives: only spheres are not in the planar table
+        const float4 q0 = g.brute[5 * e];
+        if (__float_as_uint(q0.w) != PT_KIND_SPHERE) continue;
+        const float t = hit_sphere_fast(v3(q0), g.brute[5 * e + 1].x, ro, rd, t_min, tmax);
+        if (t >= 0.0f) { tmax = t; best_id = __float_as_int(g.brute[5 * e + 4].z); }
+    }
+    if (best_id >= 0) best_t = tmax;
+}
+template <class G>
+PT_DEV bool any_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, const G& g, float3 ro, float3 rd, float t_min, float t_max) {
+    bool occluded = false;
+#define PT_STEP(k)                                                                                                            \
+    {                                                                                                                         \
+        bool oka, okb; float2 uv;                                                                                             \
+        fast_pair(fp.e + 8 * (k), ro, rd, t_min, t_max, oka, okb, uv);                                                        \
+        occluded |= oka | okb;                                                                                                \
+    }
+    PT_FAST_SCAN(n_fast_pairs, PT_STEP)
+#undef PT_STEP
+    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e) {
+        const float4 q0 = g.brute[5 * e];
+        if (__float_as_uint(q0.w) != PT_KIND_SPHERE) continue;
+        occluded |= hit_sphere_fast(v3(q0), g.brute[5 * e + 1].x, ro, rd, t_min, t_max) >= 0.0f;
+    }
+    return occluded;
+}
+
 // Closest hit.  Winner = smallest t in [t_min, inf); equal t -> higher object index (world.rs:281-287 scans
 // in index order with an inclusive t_max, so a later object replaces an earlier one on a tie).
 template <bool SMEM, bool BRUTE, class G>
@@ -509,12 +599,21 @@ inline SceneView make_scene_view(const SceneDev& d) {
 // shared memory, checked pair test; 2 = triangle pairs from the constant bank, checked; 3 = constant bank, in-domain (no
 // reciprocal range check, no `u <= 1`: pt_math.cuh).  Shared by the shared-memory wavefront and pt_trace_primary so that the
 // parity hook runs exactly the scan the render runs.
+// 4 = 3 for primary rays + the planar-entry scan (fast_pair) for shadow and scattered rays: the default of small scenes.
 inline int pick_scan_mode(const SceneDev& scene, const pt_camera& cam, uint32_t traversal) {
     const bool param_ok = scene.brute && scene.n_pairs > 0 && scene.n_pairs <= (uint32_t)kParamPairs && !scene.brute_host.empty();
     if (!param_ok || traversal == PT_TRAVERSAL_BRUTE_TABLE) return 1;
     bool in_domain = scene.fp32_domain;
     for (int k = 0; k < 3; ++k) if (!(fabsf(cam.origin[k]) <= kFp32DomainMax)) in_domain = false;
-    return (in_domain && traversal != PT_TRAVERSAL_BRUTE_PARAM_CHECKED) ? 3 : 2;
+    if (!in_domain || traversal == PT_TRAVERSAL_BRUTE_PARAM_CHECKED) return 2;
+    return (scene.n_fast_pairs > 0 && traversal != PT_TRAVERSAL_BRUTE_EXACT) ? 4 : 3;
+}
+inline FastParam make_fast_param(const SceneDev& scene) {   // right-aligned like BruteParam (PT_FAST_SCAN)
+    FastParam fp;
+    memset(&fp, 0, sizeof(fp));
+    if (scene.n_fast_pairs && scene.n_fast_pairs <= (uint32_t)kFastPairs)
+        memcpy(fp.e + 8 * ((size_t)kFastPairs - scene.n_fast_pairs), scene.fast_host.data(), sizeof(float4) * 8 * (size_t)scene.n_fast_pairs);
+    return fp;
 }
 inline BruteParam make_brute_param(const SceneDev& scene) {   // right-aligned: the scan is entered at slot kParamPairs - n_pairs (PT_PARAM_SCAN)
     BruteParam bp;

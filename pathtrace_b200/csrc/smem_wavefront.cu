@@ -78,10 +78,12 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
 
 // MODE 0: LBVH from shared memory; 1: scan table from shared memory; 2: its triangle pairs from the kernel parameter `bp`
 // (constant bank, unrolled) and only the unpaired primitives from shared memory; 3: as 2 for scenes and cameras inside the
-// FP32 coordinate domain (SceneDev::fp32_domain): the pair test without the reciprocal's range check and without `u <= 1`.
+// FP32 coordinate domain (SceneDev::fp32_domain): the pair test without the reciprocal's range check and without `u <= 1`;
+// 4: as 3 for primary rays, the planar-entry scan from the kernel parameter `fp` for shadow and scattered rays.
 template <int MODE, bool PROF>
 __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
-                                                                           const __grid_constant__ BruteParam bp) {
+                                                                           const __grid_constant__ BruteParam bp,
+                                                                           const __grid_constant__ FastParam fp, uint32_t n_fast_pairs) {
     constexpr bool BRUTE = MODE != 0;
     constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NGRP = SPT * NW;
     extern __shared__ float4 smem[];
@@ -120,11 +122,15 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         for (uint32_t i = tid; i < s.n_brute * 5; i += kSwBlock) s_brute[i] = __ldg(s.brute + i);
         g.brute = s_brute; g.n_brute = s.n_brute; g.n_pairs = s.n_pairs;
     }
-    auto trace_closest = [&](float3 ro, float3 rd, float& t, int& id) {
-        if (MODE >= 2) closest_hit_param<MODE == 2>(bp, g, ro, rd, f.t_min, t, id);
+    // MODE 4: primary rays keep the bit-exact scan (ids and t are pinned to the FP32 oracle); shadow and scattered rays take
+    // the planar-entry scan (pt_wave.cuh: fast_pair)
+    auto trace_closest = [&](float3 ro, float3 rd, bool primary, float& t, int& id) {
+        if (MODE == 4 && !primary) closest_hit_fast(fp, n_fast_pairs, g, ro, rd, f.t_min, t, id);
+        else if (MODE >= 2) closest_hit_param<MODE == 2>(bp, g, ro, rd, f.t_min, t, id);
         else closest_hit<true, BRUTE>(g, s.n_objects, ro, rd, f.t_min, t, id);
     };
     auto trace_any = [&](float3 ro, float3 rd, float t_max) -> bool {
+        if (MODE == 4) return any_hit_fast(fp, n_fast_pairs, g, ro, rd, f.t_min, t_max);
         if (MODE >= 2) return any_hit_param<MODE == 2>(bp, g, ro, rd, f.t_min, t_max);
         return any_hit<true, BRUTE>(g, s.n_objects, ro, rd, f.t_min, t_max);
     };
@@ -167,7 +173,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                     ro = s_ro[j]; rd = s_rd[j];
                 }
                 float t; int id;
-                trace_closest(v3(ro), v3(rd), t, id);
+                trace_closest(v3(ro), v3(rd), seed, t, id);
                 s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
                 if (id < 0) c = CLS_MISS;
                 else {
@@ -286,6 +292,8 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
     };
     const int mode = !brute ? 0 : pick_scan_mode(scene, rl.cam, rl.prm.traversal);
     const BruteParam bp = make_brute_param(scene);
+    const FastParam fp = make_fast_param(scene);
+    const uint32_t n_fast_pairs = scene.n_fast_pairs;
     int occ = 0, rc;
     auto with_kernel = [&](auto&& fn) -> int {
         switch (mode * 2 + (profile ? 1 : 0)) {
@@ -296,7 +304,9 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
             case 4: return fn(k_smem_wavefront<2, false>);
             case 5: return fn(k_smem_wavefront<2, true>);
             case 6: return fn(k_smem_wavefront<3, false>);
-            default: return fn(k_smem_wavefront<3, true>);
+            case 7: return fn(k_smem_wavefront<3, true>);
+            case 8: return fn(k_smem_wavefront<4, false>);
+            default: return fn(k_smem_wavefront<4, true>);
         }
     };
     rc = with_kernel([&](auto kernel) { return pick(kernel, occ); });
@@ -328,7 +338,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         while (ctx->prof_events.size() < 2) { cudaEvent_t e; PT_CUDA_CHECK(ctx, cudaEventCreate(&e)); ctx->prof_events.push_back(e); }
         PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[0], st));
     }
-    with_kernel([&](auto kernel) { kernel<<<grid, kSwBlock, smem, st>>>(sv, f, out, bp); return PT_OK; });
+    with_kernel([&](auto kernel) { kernel<<<grid, kSwBlock, smem, st>>>(sv, f, out, bp, fp, n_fast_pairs); return PT_OK; });
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     if (profile) PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[1], st));
     if (stats) {

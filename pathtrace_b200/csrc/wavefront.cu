@@ -465,6 +465,27 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary_param(SceneView s, con
     if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
 }
 
+// Parity hook for the secondary-ray scan (PT_TRAVERSAL_BRUTE_FAST): closest_hit_fast applied to primary rays.
+__global__ void __launch_bounds__(kBlock) k_trace_primary_fast(SceneView s, const __grid_constant__ Frame f, int jitter, float ox, float oy, uint32_t sample,
+                                                               int32_t* __restrict__ obj, float* __restrict__ tt, float* __restrict__ dirs,
+                                                               const __grid_constant__ FastParam fp, uint32_t n_fast_pairs) {
+    extern __shared__ float4 smem[];
+    Geo<true> g = stage_scene<true>(s, smem, false);
+    uint32_t i = blockIdx.x * kBlock + threadIdx.x;
+    if (i >= f.npix) return;
+    uint32_t x = i % f.cam.width, y = i / f.cam.width;
+    if (jitter) {
+        uint4 r = philox4x32_10(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+        ox = u01(r.x); oy = u01(r.y);
+    }
+    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
+    float t; int id;
+    closest_hit_fast(fp, n_fast_pairs, g, f.cam.origin, d, f.t_min, t, id);
+    obj[i] = id;
+    tt[i] = id >= 0 ? t : __int_as_float(0x7f800000);
+    if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
+}
+
 // pt_render_moments: total += batch, moment2 += batch^2, batch = 0
 __global__ void k_fold_moments(float4* __restrict__ batch, float4* __restrict__ total, float4* __restrict__ m2, uint32_t npix) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -567,9 +588,18 @@ int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_cam
     Mode mode = pick_mode(scene, prm.traversal);
     uint32_t grid = (f.npix + kBlock - 1) / kBlock;
     const int scan = (mode.brute && mode.smem && scene.brute) ? pick_scan_mode(scene, cam, prm.traversal) : 0;
+    if (prm.traversal == PT_TRAVERSAL_BRUTE_FAST) {
+        if (scan != 4) { ctx->err = "PT_TRAVERSAL_BRUTE_FAST: this scene has no planar-entry table (too many triangles, or outside the FP32 coordinate domain)"; return PT_ERR_INVALID; }
+        const FastParam fp = make_fast_param(scene);
+        int rc = set_smem(ctx, k_trace_primary_fast, mode.smem_bytes); if (rc) return rc;
+        k_trace_primary_fast<<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, fp, scene.n_fast_pairs);
+        PT_CUDA_CHECK(ctx, cudaGetLastError());
+        if (launches) *launches += 1;
+        return PT_OK;
+    }
     if (scan >= 2) {   // the constant-bank scan the shared-memory wavefront runs on this scene
         const BruteParam bp = make_brute_param(scene);
-        if (scan == 2) {
+        if (scan == 2) {   // (scan 3 and 4 trace primary rays with the same in-domain pair test)
             int rc = set_smem(ctx, k_trace_primary_param<true>, mode.smem_bytes); if (rc) return rc;
             k_trace_primary_param<true><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp);
         } else {

@@ -52,7 +52,7 @@ def test_lbvh_trivial(n, oracle, gpu_ctx):
 
 
 @pytest.mark.parametrize("name", ["default", "zoo", "spheres", "random2", "random17", "random300", "random5000"])
-@pytest.mark.parametrize("traversal", ["bvh", "brute", "brute_table", "brute_param_checked"])
+@pytest.mark.parametrize("traversal", ["bvh", "brute", "brute_exact", "brute_table", "brute_param_checked"])
 @pytest.mark.parametrize("jitter", [False, True])
 def test_primary_hits(name, traversal, jitter, oracle, gpu_ctx):
     """`brute` is the scan the render (and the benchmark) runs on that scene: for the default scene and the zoo the triangle
@@ -62,7 +62,7 @@ def test_primary_hits(name, traversal, jitter, oracle, gpu_ctx):
     sh, mt, cam = _scenes()[name]
     if traversal.startswith("brute") and len(sh) > 1000:
         pytest.skip("brute force over 5000 objects is covered by the bvh run")
-    if traversal in ("brute_table", "brute_param_checked") and name not in ("default", "zoo", "random17"):
+    if traversal in ("brute_exact", "brute_table", "brute_param_checked") and name not in ("default", "zoo", "random17"):
         pytest.skip("the forced scan forms are exercised on the scenes whose pairs fit the constant bank")
     ocam = oracle_camera(oracle, cam)
     sc = api.Scene(gpu_ctx, sh, mt)
@@ -98,8 +98,9 @@ def test_smem_wavefront_equals_hbm_wavefront(scene_name, strategy, gpu_ctx):
     sh, mt, cam = _scenes()[scene_name]
     sc = api.Scene(gpu_ctx, sh, mt)
     out = {}
+    trav = "brute_exact" if scene_name == "default" else "auto"     # the bit-exact scan on both sides (scan mode 3 / LBVH)
     for hbm in (False, True):
-        out[hbm] = api.render(gpu_ctx, sc, cam, api.render_params(spp=48, strategy=strategy, hbm_queues=hbm, sample_offset=5))
+        out[hbm] = api.render(gpu_ctx, sc, cam, api.render_params(spp=48, strategy=strategy, hbm_queues=hbm, sample_offset=5, traversal=trav))
     sc.close()
     (ra, ga, sa), (rb, gb, sb) = out[False], out[True]
     if scene_name != "spheres":     # 495 objects + LBVH do not fit the shared-memory formulation: both runs take the HBM path
@@ -195,21 +196,24 @@ def test_single_samples_match_fp32_oracle(hbm_queues, oracle, gpu_ctx):
 
 
 def test_benchmark_scan_mode_is_the_one_trace_primary_checks(gpu_ctx):
-    """The default scene renders through scan mode 3 (constant-bank pairs, in-domain pair test); `brute_table` and
-    `brute_param_checked` select modes 1 and 2; all three trace the same paths."""
+    """The default scene renders through scan mode 4 (primary rays: constant-bank pairs, in-domain pair test; shadow and
+    scattered rays: planar entries); `brute_exact`, `brute_param_checked` and `brute_table` select the bit-exact modes 3, 2
+    and 1, which trace the same paths as the LBVH walk."""
     from pathtrace_b200 import api, scenes
     sh, mt, cam = scenes.default_scene(96, 64)
     sc = api.Scene(gpu_ctx, sh, mt)
     out = {}
-    for trav, mode in (("auto", 3), ("brute", 3), ("brute_param_checked", 2), ("brute_table", 1), ("bvh", 0)):
+    for trav, mode in (("auto", 4), ("brute", 4), ("brute_exact", 3), ("brute_param_checked", 2), ("brute_table", 1), ("bvh", 0)):
         rad, _, st = api.render(gpu_ctx, sc, cam, api.render_params(spp=8, traversal=trav))
         assert st["scan_mode"] == mode and st["n_kernel"]["smem_wavefront"] == 1, (trav, st["scan_mode"])
         out[trav] = (rad, st)
     sc.close()
-    for trav in ("brute", "brute_param_checked", "brute_table", "bvh"):
+    for trav in ("brute_param_checked", "brute_table", "bvh"):           # the bit-exact forms trace the very same paths
         for k in ("rays_primary", "rays_shadow", "rays_scattered", "path_vertices"):
-            assert out[trav][1][k] == out["auto"][1][k], (trav, k)
-        assert np.allclose(out[trav][0], out["auto"][0], rtol=1e-4, atol=1e-5)
+            assert out[trav][1][k] == out["brute_exact"][1][k], (trav, k)
+        assert np.allclose(out[trav][0], out["brute_exact"][0], rtol=1e-4, atol=1e-5)
+    assert out["brute"][1]["rays_primary"] == out["brute_exact"][1]["rays_primary"]
+    assert abs(out["brute"][1]["rays_scattered"] - out["brute_exact"][1]["rays_scattered"]) <= 1e-3 * out["brute_exact"][1]["rays_scattered"]
 
 
 @pytest.mark.parametrize("n", [0, 1])
