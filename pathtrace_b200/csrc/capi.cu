@@ -81,7 +81,7 @@ void build_fast_table(const pt_shape* shapes, uint32_t n, SceneDev& out) {
         for (double v : e.m) if (!std::isfinite(v) || std::fabs(v) > 1e18) return false;
         return true;
     };
-    out.fast_host.clear(); out.n_fast_pairs = 0;
+    out.fast_host.clear(); out.n_fast_pairs = 0; out.n_fast_spheres = 0;
     bool ok = true;
     for (uint32_t i = 0; i < n && ok; ++i) {
         if (shapes[i].kind != PT_SHAPE_TRIANGLE) continue;
@@ -119,6 +119,16 @@ void build_fast_table(const pt_shape* shapes, uint32_t n, SceneDev& out) {
         entries.push_back(e);
     }
     if (entries.empty() || entries.size() > 2u * kFastParamPairs) return;
+    uint32_t n_sph = 0;
+    for (uint32_t i = 0; i < n; ++i) n_sph += shapes[i].kind == PT_SHAPE_SPHERE;
+    if (n_sph > (uint32_t)kFastParamSpheres) return;
+    for (uint32_t i = 0; i < n; ++i)
+        if (shapes[i].kind == PT_SHAPE_SPHERE) {
+            out.fast_spheres[out.n_fast_spheres] = make_float4(shapes[i].v[0], shapes[i].v[1], shapes[i].v[2], shapes[i].v[3]);
+            out.fast_sphere_ids[out.n_fast_spheres++] = (int)i;
+        }
+    // (u, v) are stored centred: the unit square becomes [-1/2, 1/2]^2 (one |.| <= 1/2 test), u + v <= lim becomes u' + v' <= lim - 1
+    for (Entry& e : entries) { e.m[3] -= 0.5; e.m[7] -= 0.5; e.lim -= 1.0f; }
     if (entries.size() & 1u) { Entry d; for (double& v : d.m) v = 0.0; d.m[11] = 1.0; d.id_a = d.id_b = -1; d.lim = 0.0f; entries.push_back(d); }   // w == 1 everywhere: never hit
     out.n_fast_pairs = (uint32_t)entries.size() / 2;
     out.fast_host.resize(8 * (size_t)out.n_fast_pairs);

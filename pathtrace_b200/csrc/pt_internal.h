@@ -11,6 +11,7 @@
 constexpr float kFp32DomainMax = 4294967296.0f;   // 2^32, see SceneDev::fp32_domain
 constexpr int kBruteParamPairs = 8;   // pair entries of the scan table that can travel as a kernel parameter (pt_wave.cuh: BruteParam)
 constexpr int kFastParamPairs = 4;    // pairs of planar entries (parallelograms / triangles) of the secondary-ray scan (pt_wave.cuh: FastParam)
+constexpr int kFastParamSpheres = 4;  // spheres that travel with them
 
 // Scene resident in HBM (replicated per GPU).  All arrays are float4-packed for 128-bit loads.
 struct SceneDev {
@@ -31,6 +32,9 @@ struct SceneDev {
     // when the scene's triangles do not fit kFastParamPairs pairs (the exact scan then serves every ray).
     std::vector<float4> fast_host;
     uint32_t n_fast_pairs = 0;
+    float4 fast_spheres[kFastParamSpheres] = {};   // (center, radius) and object ids of the scene's spheres when they all fit
+    int fast_sphere_ids[kFastParamSpheres] = {};
+    uint32_t n_fast_spheres = 0;
     uint32_t* codes_sorted = nullptr;
     uint32_t* prim_sorted = nullptr;
     float bounds[6] = {0, 0, 0, 0, 0, 0};

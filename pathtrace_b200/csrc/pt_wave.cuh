@@ -27,6 +27,7 @@ struct Frame {
     uint32_t k0, k1;         // Philox key
     float t_min;
     float4* accum;           // per pixel: sum r, g, b, (reserved)
+    float3 blo, bhi;         // padded scene bounds (SceneDev::bounds); blo.x > bhi.x: none
 };
 
 struct SceneView {
@@ -173,7 +174,17 @@ PT_DEV bool any_hit_param(const BruteParam& bp, const G& g, float3 ro, float3 rd
 // (PT_TRAVERSAL_BRUTE_FAST): ids equal except on edges, t within 1e-5.
 constexpr int kFastPairs = kFastParamPairs;
 static_assert(kFastPairs == 4, "PT_FAST_SCAN below is written for 4 slots");
-struct FastParam { float4 e[8 * kFastPairs]; };
+constexpr int kFastSpheres = kFastParamSpheres;
+static_assert(kFastSpheres == 4, "PT_FAST_SPHERES below is written for 4 slots");
+struct FastParam { float4 e[8 * kFastPairs]; float4 sph[kFastSpheres]; int sph_id[kFastSpheres]; };   // spheres right-aligned like the pairs
+#define PT_FAST_SPHERES(n, STEP)                                                                                              \
+    switch (n) {                                                                                                              \
+        case 4: STEP(0) [[fallthrough]];                                                                                      \
+        case 3: STEP(1) [[fallthrough]];                                                                                      \
+        case 2: STEP(2) [[fallthrough]];                                                                                      \
+        case 1: STEP(3) [[fallthrough]];                                                                                      \
+        default: break;                                                                                                       \
+    }
 #define PT_FAST_SCAN(n_pairs, STEP)                                                                                           \
     switch (n_pairs) {                                                                                                        \
         case 4: STEP(0) [[fallthrough]];                                                                                      \
@@ -196,8 +207,9 @@ PT_DEV float2 fast_pair(const float4* E, float3 ro, float3 rd, float t_min, floa
     const float2 v = __ffma2_rn(t, row_d(E[2], E[3]), row_o(E[2], E[3]));
     uv = __fadd2_rn(u, v);
     // a ray parallel to the plane gives t = +-inf or NaN: refused by the range test (t_max <= FLT_MAX)
-    ok_a = (fminf(u.x, v.x) >= 0.0f) & (fmaxf(u.x, v.x) <= 1.0f) & (uv.x <= E[7].x) & (t.x >= t_min) & (t.x <= t_max);
-    ok_b = (fminf(u.y, v.y) >= 0.0f) & (fmaxf(u.y, v.y) <= 1.0f) & (uv.y <= E[7].y) & (t.y >= t_min) & (t.y <= t_max);
+    // (u, v) are centred on the entry: the unit square is |u|, |v| <= 1/2 and `u + v <= 1` of a triangle is uv <= 0 (E[7] = lim - 1)
+    ok_a = (fmaxf(fabsf(u.x), fabsf(v.x)) <= 0.5f) & (uv.x <= E[7].x) & (t.x >= t_min) & (t.x <= t_max);
+    ok_b = (fmaxf(fabsf(u.y), fabsf(v.y)) <= 0.5f) & (uv.y <= E[7].y) & (t.y >= t_min) & (t.y <= t_max);
     return t;
 }
 // shape.rs:53-89 without the correctly rounded divisions and square root of hit_sphere (same cancellation-free quadratic)
@@ -215,7 +227,7 @@ PT_DEV float hit_sphere_fast(float3 c, float radius, float3 ro, float3 rd, float
     return (disc < 0.0f || !(near_ok || far_ok)) ? -1.0f : (near_ok ? t_near : t_far);
 }
 template <class G>
-PT_DEV void closest_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, const G& g, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
+PT_DEV void closest_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, uint32_t n_fast_spheres, const G& g, float3 ro, float3 rd, float t_min, float& best_t, int& best_id) {
     best_t = FLT_MAX; best_id = -1;
     float tmax = FLT_MAX;
 #define PT_STEP(k)                                                                                                            \
@@ -223,21 +235,23 @@ PT_DEV void closest_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, const G
         bool oka, okb; float2 uv;                                                                                             \
         const float2 t = fast_pair(fp.e + 8 * (k), ro, rd, t_min, tmax, oka, okb, uv);                                        \
         const float4 ids = fp.e[8 * (k) + 6];                                                                                 \
-        if (oka) { tmax = t.x; best_id = __float_as_int(uv.x <= 1.0f ? ids.x : ids.z); }                                      \
-        if (okb & (t.y <= tmax)) { tmax = t.y; best_id = __float_as_int(uv.y <= 1.0f ? ids.y : ids.w); }                      \
+        if (oka) { tmax = t.x; best_id = __float_as_int(uv.x <= 0.0f ? ids.x : ids.z); }                                      \
+        if (okb & (t.y <= tmax)) { tmax = t.y; best_id = __float_as_int(uv.y <= 0.0f ? ids.y : ids.w); }                      \
     }
     PT_FAST_SCAN(n_fast_pairs, PT_STEP)
 #undef PT_STEP
-    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e) {            // the unpaired primitives: only spheres are not in the planar table
-        const float4 q0 = g.brute[5 * e];
-        if (__float_as_uint(q0.w) != PT_KIND_SPHERE) continue;
-        const float t = hit_sphere_fast(v3(q0), g.brute[5 * e + 1].x, ro, rd, t_min, tmax);
-        if (t >= 0.0f) { tmax = t; best_id = __float_as_int(g.brute[5 * e + 4].z); }
+    (void)g;
+#define PT_STEP(k)                                                                                                            \
+    {                                                                                                                         \
+        const float t = hit_sphere_fast(v3(fp.sph[k]), fp.sph[k].w, ro, rd, t_min, tmax);                                     \
+        if (t >= 0.0f) { tmax = t; best_id = fp.sph_id[k]; }                                                                  \
     }
+    PT_FAST_SPHERES(n_fast_spheres, PT_STEP)
+#undef PT_STEP
     if (best_id >= 0) best_t = tmax;
 }
 template <class G>
-PT_DEV bool any_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, const G& g, float3 ro, float3 rd, float t_min, float t_max) {
+PT_DEV bool any_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, uint32_t n_fast_spheres, const G& g, float3 ro, float3 rd, float t_min, float t_max) {
     bool occluded = false;
 #define PT_STEP(k)                                                                                                            \
     {                                                                                                                         \
@@ -247,11 +261,10 @@ PT_DEV bool any_hit_fast(const FastParam& fp, uint32_t n_fast_pairs, const G& g,
     }
     PT_FAST_SCAN(n_fast_pairs, PT_STEP)
 #undef PT_STEP
-    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e) {
-        const float4 q0 = g.brute[5 * e];
-        if (__float_as_uint(q0.w) != PT_KIND_SPHERE) continue;
-        occluded |= hit_sphere_fast(v3(q0), g.brute[5 * e + 1].x, ro, rd, t_min, t_max) >= 0.0f;
-    }
+    (void)g;
+#define PT_STEP(k) occluded |= hit_sphere_fast(v3(fp.sph[k]), fp.sph[k].w, ro, rd, t_min, t_max) >= 0.0f;
+    PT_FAST_SPHERES(n_fast_spheres, PT_STEP)
+#undef PT_STEP
     return occluded;
 }
 
@@ -613,6 +626,10 @@ inline FastParam make_fast_param(const SceneDev& scene) {   // right-aligned lik
     memset(&fp, 0, sizeof(fp));
     if (scene.n_fast_pairs && scene.n_fast_pairs <= (uint32_t)kFastPairs)
         memcpy(fp.e + 8 * ((size_t)kFastPairs - scene.n_fast_pairs), scene.fast_host.data(), sizeof(float4) * 8 * (size_t)scene.n_fast_pairs);
+    for (uint32_t k = 0; k < scene.n_fast_spheres; ++k) {
+        fp.sph[kFastSpheres - scene.n_fast_spheres + k] = scene.fast_spheres[k];
+        fp.sph_id[kFastSpheres - scene.n_fast_spheres + k] = scene.fast_sphere_ids[k];
+    }
     return fp;
 }
 inline BruteParam make_brute_param(const SceneDev& scene) {   // right-aligned: the scan is entered at slot kParamPairs - n_pairs (PT_PARAM_SCAN)
@@ -635,6 +652,7 @@ inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* a
     f.k0 = (uint32_t)p.seed; f.k1 = (uint32_t)(p.seed >> 32);
     f.t_min = p.t_min;
     f.accum = accum;
+    f.blo = make_float3(1.f, 1.f, 1.f); f.bhi = make_float3(-1.f, -1.f, -1.f);
     return f;
 }
 

@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary_param(SceneView s, con
 // Parity hook for the secondary-ray scan (PT_TRAVERSAL_BRUTE_FAST): closest_hit_fast applied to primary rays.
 __global__ void __launch_bounds__(kBlock) k_trace_primary_fast(SceneView s, const __grid_constant__ Frame f, int jitter, float ox, float oy, uint32_t sample,
                                                                int32_t* __restrict__ obj, float* __restrict__ tt, float* __restrict__ dirs,
-                                                               const __grid_constant__ FastParam fp, uint32_t n_fast_pairs) {
+                                                               const __grid_constant__ FastParam fp, uint32_t n_fast_pairs, uint32_t n_fast_spheres) {
     extern __shared__ float4 smem[];
     Geo<true> g = stage_scene<true>(s, smem, false);
     uint32_t i = blockIdx.x * kBlock + threadIdx.x;
@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary_fast(SceneView s, cons
     }
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
     float t; int id;
-    closest_hit_fast(fp, n_fast_pairs, g, f.cam.origin, d, f.t_min, t, id);
+    closest_hit_fast(fp, n_fast_pairs, n_fast_spheres, g, f.cam.origin, d, f.t_min, t, id);
     obj[i] = id;
     tt[i] = id >= 0 ? t : __int_as_float(0x7f800000);
     if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
@@ -592,7 +592,7 @@ int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_cam
         if (scan != 4) { ctx->err = "PT_TRAVERSAL_BRUTE_FAST: this scene has no planar-entry table (too many triangles, or outside the FP32 coordinate domain)"; return PT_ERR_INVALID; }
         const FastParam fp = make_fast_param(scene);
         int rc = set_smem(ctx, k_trace_primary_fast, mode.smem_bytes); if (rc) return rc;
-        k_trace_primary_fast<<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, fp, scene.n_fast_pairs);
+        k_trace_primary_fast<<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, fp, scene.n_fast_pairs, scene.n_fast_spheres);
         PT_CUDA_CHECK(ctx, cudaGetLastError());
         if (launches) *launches += 1;
         return PT_OK;

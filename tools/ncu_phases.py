@@ -36,7 +36,11 @@ def main():
     rows = list(csv.reader(io.StringIO(txt)))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[hi]
-    body = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+    body = []
+    for r in rows[hi + 1:]:             # first matching launch only
+        if len(r) != len(hdr) or r[0] == "Address":
+            break
+        body.append(r)
     ci, hs, ct, cs = hdr.index("Instructions Executed"), hdr.index("Source"), hdr.index("Thread Instructions Executed"), hdr.index("# Samples")
     tab = ncu_lines.line_table(kre)
     if len(tab) != len(body):
