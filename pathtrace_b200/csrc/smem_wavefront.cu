@@ -36,14 +36,16 @@ using namespace ptw;
 
 namespace {
 
-// One CTA of 896 threads per SM owning 2688 slots: the class sort sees a window wide enough that almost every 32-slot tile
-// is a single class (measured: 512-slot windows lose ~12 % to mixed tiles), 3 rays per thread keep phase T balanced, and 72
-// registers per thread beat 1024 threads at 64 (4.32 vs 4.07 Gsamples/s: fewer spills around the unrolled scan).
+// One CTA of 768 threads per SM owning 3072 slots: the class sort sees a window wide enough that almost every 32-slot tile
+// is a single class (measured: 512-slot windows lose ~12 % to mixed tiles).  Shapes measured in round 2 (threads x slots per
+// thread, Gsamples/s at 128 spp): 896 x 3 (72 registers) 6.65, 768 x 4 (80) 6.75, 640 x 5 (96) 6.76, 704 x 4 6.61, 640 x 4 6.58,
+// 576 x 5 6.44, 800 x 4 6.25, 1024 x 3 (64 registers, spills) 6.23, 960 x 3 6.05.  Phase T with dynamic 32-entry tiles (like
+// phase A) instead of a static entry per thread and group: 6.69 against 6.75.
 #ifndef PT_SW_BLOCK
-#define PT_SW_BLOCK 896
+#define PT_SW_BLOCK 768
 #endif
 #ifndef PT_SW_SPT
-#define PT_SW_SPT 3
+#define PT_SW_SPT 4
 #endif
 #ifndef PT_SW_MIN_BLOCKS
 #define PT_SW_MIN_BLOCKS 1
