@@ -26,16 +26,24 @@ PT_DEV Mat load_mat(const float4* __restrict__ mats, int obj) {
 // material.rs:51-53, mirror.rs:317-319
 PT_DEV float mat_eta(const Mat& m) { return m.kind == PT_MATK_MIRROR ? m.ior : 1.0f; }
 
-// Shared tangent frame: material.rs:105-119, mirror.rs:21-27, material.rs:215-222
+// Shared tangent frame: material.rs:105-119, mirror.rs:21-27, material.rs:215-222.  up x n written out for the two axes
+// `up` can be (the products with its 0 and 1 components are exact, so this is the reference's cross product).
 PT_DEV void tangent_frame(float3 n, float3& tg, float3& bt) {
-    float3 up = fabsf(n.y) > 0.999f ? v3(1.f, 0.f, 0.f) : v3(0.f, 1.f, 0.f);
-    tg = normalize(cross(up, n));
+    const bool up_x = fabsf(n.y) > 0.999f;
+    tg = normalize(up_x ? v3(0.f, -n.z, n.y) : v3(n.z, 0.f, -n.x));
     bt = cross(n, tg);
+}
+// sin and cos of 2 pi r for r in (0, 1): the argument is folded to (-pi, pi), where MUFU.SIN / MUFU.COS are accurate to
+// 2^-21 absolute — far inside what a sampled direction needs (the library's sin-cos-of-pi-x costs ~30 instructions, this 6).
+PT_DEV void sincos_2pi(float r, float& s, float& c) {
+    const float phi = (r - 0.5f) * (2.0f * PT_PI);
+    s = -__sinf(phi);
+    c = -__cosf(phi);
 }
 // material.rs:93-122 / :268-295 — phi from r1, cos(theta) = sqrt(r2)
 PT_DEV float3 cosine_sample(float3 n, float r1, float r2) {
     float sp, cp;
-    sincospif(2.0f * r1, &sp, &cp);
+    sincos_2pi(r1, sp, cp);
     float ct = sqrtf(r2);
     float st = sqrtf(fmaxf(1.0f - ct * ct, 0.0f));
     float3 tg, bt;
@@ -78,7 +86,7 @@ PT_DEV float3 sample_ggx_vndf(const Mat& m, float3 view, float3 n, float r1, flo
     float3 t2 = cross(vh, t1);
     float r = sqrtf(r1);
     float sp, cp;
-    sincospif(2.0f * r2, &sp, &cp);
+    sincos_2pi(r2, sp, cp);
     float c1 = r * cp, c2 = r * sp;
     float s = 0.5f * (1.0f + vh.z);
     c2 = (1.0f - s) * sqrtf(fmaxf(1.0f - c1 * c1, 0.0f)) + s * c2;
@@ -231,7 +239,7 @@ PT_DEV void sample_light_shape(float4 q0, float4 q1, float4 q2, float4 q3, float
         float ct = 1.0f - r1 + r1 * cos_max;
         float st = sqrtf(fmaxf(1.0f - ct * ct, 0.0f));
         float sp, cp;
-        sincospif(2.0f * r2, &sp, &cp);
+        sincos_2pi(r2, sp, cp);
         float3 w = normalize(tc);
         float3 up = fabsf(w.y) > 0.999f ? v3(1.f, 0.f, 0.f) : v3(0.f, 1.f, 0.f);
         float3 uu = normalize(cross(up, w));
