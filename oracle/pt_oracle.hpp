@@ -20,7 +20,7 @@
 // Third-party arithmetic absent from /root/reference: rand 0.9.2 / rand_chacha 0.9.0 /
 // rand_core 0.9.3 (Cargo.lock:1092-1115; StdRng = ChaCha12).  Not restated: the north star
 // mandates a counter-based RNG, so image parity is distributional.  The RNG here is
-// Philox4x32-10 (Salmon et al., SC'11), pinned by the published Random123 known-answer vectors.
+// Philox4x32-7 (Salmon et al., SC'11); its round function is pinned by the published Random123 10-round known answers.
 //
 // Templated on the scalar type T:
 //   double          — the reference's numerics (image oracle, timed CPU baseline)
@@ -130,7 +130,7 @@ template <class T> struct Vec3 {
 template <class T> inline Vec3<T> operator*(T s, const Vec3<T>& v) { return v * s; }   // math.rs:186-192
 
 // ----------------------------------------------------------------------------------------------
-// Counter-based RNG: Philox4x32-10.  Replaces rand::StdRng (main.rs:51-52) by design.
+// Counter-based RNG: Philox4x32 (7 rounds in the render).  Replaces rand::StdRng (main.rs:51-52) by design.
 // key = (seed_lo, seed_hi); counter = (pixel, sample, depth, block).
 // Slot map (SURVEY Appendix A.5 draw order):
 //   camera : depth=0xFFFFFFFF block 0 -> [ox, oy, -, -]                      world.rs:299
@@ -138,9 +138,10 @@ template <class T> inline Vec3<T> operator*(T s, const Vec3<T>& v) { return v * 
 //   vertex d block 1 -> [bsdf r2, lobe u, rr u, -]                           mirror.rs:232, rendering.rs:100
 // ----------------------------------------------------------------------------------------------
 struct U4 { uint32_t w[4]; };
-inline U4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+template <int R>
+inline U4 philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
-    for (int r = 0; r < 10; ++r) {
+    for (int r = 0; r < R; ++r) {
         uint64_t p0 = (uint64_t)M0 * c0, p1 = (uint64_t)M1 * c2;
         uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
         uint32_t n1 = (uint32_t)p1;
@@ -151,6 +152,10 @@ inline U4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint
     }
     return U4{{c0, c1, c2, c3}};
 }
+// The render draws from the 7-round variant (the fastest Crush-resistant one, SC'11 Table 2), like the device; the 10-round
+// instantiation exists for the published known answers, which pin the round function both share.
+constexpr int kRngRounds = 7;
+inline U4 rng_block(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) { return philox4x32<kRngRounds>(c0, c1, c2, c3, k0, k1); }
 // 23-bit uniform in the open interval (0,1): ((x>>9)+0.5)/2^23 — exact in float and double.
 // (rand's random::<f64>() is [0,1) with 53 bits; the open interval avoids r=0 singularities
 //  that are 2^-53-rare in the reference but would be 2^-23-common in FP32)
@@ -164,7 +169,7 @@ inline uint32_t light_word(const U4& b) { return (b.w[0] & 0xffu) | ((b.w[1] & 0
 
 struct RngKey {
     uint32_t k0, k1, pixel, sample;
-    U4 block(uint32_t depth, uint32_t b) const { return philox4x32_10(pixel, sample, depth, b, k0, k1); }
+    U4 block(uint32_t depth, uint32_t b) const { return rng_block(pixel, sample, depth, b, k0, k1); }
 };
 
 // ----------------------------------------------------------------------------------------------

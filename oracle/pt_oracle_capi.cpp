@@ -68,8 +68,9 @@ void render_t(const CameraDesc& cam, const SD* sh, const MD* mt, uint32_t n, con
 
 extern "C" {
 
-void pto_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
-    U4 r = philox4x32_10(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1]);
+// rounds: 10 (the published known answers) or 7 (what the render draws from)
+void pto_philox4x32(int rounds, const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+    U4 r = rounds == 10 ? philox4x32<10>(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1]) : philox4x32<7>(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1]);
     std::memcpy(out, r.w, 16);
 }
 void pto_u01(uint32_t x, float* f, double* d) { *f = u01<float>(x); *d = u01<double>(x); }

@@ -65,9 +65,11 @@ def _p(a, t=C.c_void_p):
     return a.ctypes.data_as(t) if a is not None else None
 
 
-def philox(ctr, key):
+def philox(ctr, key, rounds=10):
+    """Philox4x32 with 10 rounds (the published known answers) or 7 (the variant the render draws from)."""
+    assert rounds in (7, 10)
     c = np.asarray(ctr, dtype=np.uint32); k = np.asarray(key, dtype=np.uint32); o = np.zeros(4, np.uint32)
-    lib().pto_philox4x32_10(_p(c), _p(k), _p(o))
+    lib().pto_philox4x32(C.c_int(rounds), _p(c), _p(k), _p(o))
     return o
 
 

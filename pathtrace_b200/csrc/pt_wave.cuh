@@ -44,7 +44,7 @@ PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uin
     uint32_t sample = f.sample_offset + (uint32_t)(w / f.npix);
     uint32_t pixel = (uint32_t)(w % f.npix);
     uint32_t x = pixel % f.cam.width, y = pixel / f.cam.width;
-    uint4 r = philox4x32_10(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+    uint4 r = rng_block(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, u01(r.x), u01(r.y));   // world.rs:299
     ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
     rd = make_float4(d.x, d.y, d.z, 0.0f);
@@ -548,9 +548,9 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
     // block 0 = [light r1, light r2, bsdf r1, bsdf r2] (+ the light pick from the low byte of each word); block 1 =
     // [lobe u, roulette u]: only GGX surfaces choose a lobe and roulette starts at min_depth (q == 1 before), so most vertices
     // never generate it.
-    uint4 b0 = philox4x32_10(pixel, sample, depth, 0u, f.k0, f.k1);
+    uint4 b0 = rng_block(pixel, sample, depth, 0u, f.k0, f.k1);
     uint4 b1 = make_uint4(0u, 0u, 0u, 0u);
-    if (m.kind == PT_MATK_MIRROR || depth >= f.min_depth) b1 = philox4x32_10(pixel, sample, depth, 1u, f.k0, f.k1);
+    if (m.kind == PT_MATK_MIRROR || depth >= f.min_depth) b1 = rng_block(pixel, sample, depth, 1u, f.k0, f.k1);
     // ---- NEE (rendering.rs:53-81, world.rs:251-267); visibility resolved by the shadow stage
     bool want_shadow = false;
     if (mis && sc.n_lights > 0) {

@@ -432,7 +432,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary(SceneView s, const __g
     if (i >= f.npix) return;
     uint32_t x = i % f.cam.width, y = i / f.cam.width;
     if (jitter) {
-        uint4 r = philox4x32_10(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+        uint4 r = rng_block(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
         ox = u01(r.x); oy = u01(r.y);
     }
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary_param(SceneView s, con
     if (i >= f.npix) return;
     uint32_t x = i % f.cam.width, y = i / f.cam.width;
     if (jitter) {
-        uint4 r = philox4x32_10(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+        uint4 r = rng_block(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
         ox = u01(r.x); oy = u01(r.y);
     }
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
@@ -475,7 +475,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary_fast(SceneView s, cons
     if (i >= f.npix) return;
     uint32_t x = i % f.cam.width, y = i / f.cam.width;
     if (jitter) {
-        uint4 r = philox4x32_10(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+        uint4 r = rng_block(i, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
         ox = u01(r.x); oy = u01(r.y);
     }
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
