@@ -15,7 +15,7 @@ import tempfile
 from collections import defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB = os.path.join(ROOT, "pathtrace_b200", "lib", "libpathtrace_b200.so")
+LIB = os.environ.get("NCU_LIB") or os.path.join(ROOT, "pathtrace_b200", "lib", "libpathtrace_b200.so")
 
 
 def line_table(kernel_re):
