@@ -116,6 +116,136 @@ def oracle_cam(O, cam):
     return c
 
 
+# ------------------------------------------------------------------------------------------ other configurations
+def _frame(api, dist, torch, ctx, scene, cam, spp, rank, world, ext, dev, reps=2, **kw):
+    """One frame of `spp` samples per pixel split over the ranks (spp split + one reduce + resolve on rank 0), device
+    resident, CUDA events on the library stream, max over ranks; best of `reps`.  Returns (ms, stats of this rank)."""
+    from pathtrace_b200.distributed import split_spp
+    W, H = cam.width, cam.height
+    spp_g, off_g = split_spp(spp, world, rank)
+    with torch.cuda.stream(ext):
+        accum = torch.empty(W * H, 4, device=dev, dtype=torch.float32)
+        rgba = torch.empty(W * H, 4, device=dev, dtype=torch.uint8)
+    best, st_best = None, None
+    for _ in range(reps + 1):                      # first pass = warm-up
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        st = None
+        with torch.cuda.stream(ext):
+            e0.record(ext)
+            accum.zero_()
+            if spp_g:
+                st = api.render_accumulate_device(ctx, scene, cam, api.render_params(spp=spp_g, sample_offset=off_g, **kw), accum.data_ptr())
+            if world > 1:
+                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                api.resolve_device(ctx, accum.data_ptr(), W, H, spp, 0, rgba.data_ptr())
+            e1.record(ext)
+        ext.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        if best is None or ms.item() < best:
+            best, st_best = float(ms.item()), st
+    return best, st_best
+
+
+def _sum_over_ranks(torch, dist, dev, world, st, keys):
+    v = torch.tensor([float(st[k]) if st else 0.0 for k in keys], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(v, op=dist.ReduceOp.SUM)
+    return dict(zip(keys, v.tolist()))
+
+
+def other_configs(args, rank, world, ctx, ext, dev):
+    """BASELINE.json configs[2..4] next to the headline (configs[1]): each at its own resolution and object count with spp
+    reduced so that the whole block stays under a minute.  Not bench lines of their own — sub-records of the one JSON line."""
+    import torch
+    import torch.distributed as dist
+    from pathtrace_b200 import api, scenes
+    peaks, peaks_src = measured_peaks()
+    keys = ("samples", "rays_primary", "rays_shadow", "rays_scattered", "path_vertices", "kernel_launches", "nodes_visited", "prim_tests")
+    out = {}
+
+    # ---- C3: 495-object random spheres, 3840x2160 (formulation B, LBVH in shared memory)
+    sh, mt, cam = scenes.random_spheres_scene(3840, 2160)
+    sc = api.Scene(ctx, sh, mt)
+    spp = args.c3_spp
+    ms, st = _frame(api, dist, torch, ctx, sc, cam, spp, rank, world, ext, dev)
+    tot = _sum_over_ranks(torch, dist, dev, world, st, keys)
+    _, stc = _frame(api, dist, torch, ctx, sc, cam, max(world, 4), rank, world, ext, dev, reps=0, counters=True)   # node / primitive counters (slower pass)
+    cnt = _sum_over_ranks(torch, dist, dev, world, stc, keys)
+    rays_c = max(cnt["rays_primary"] + cnt["rays_shadow"] + cnt["rays_scattered"], 1.0)
+    rays = tot["rays_primary"] + tot["rays_shadow"] + tot["rays_scattered"]
+    # algorithmic flops of a BVH scene (SURVEY 8d): nodes visited x 2 box tests x 18 + primitive tests x the oracle's per-test
+    # cost + shading per vertex; per-ray averages from the counter pass
+    fl_node, fl_prim, fl_shade = 36.0, 40.0, 320.0
+    flops = rays * (cnt["nodes_visited"] / rays_c * fl_node + cnt["prim_tests"] / rays_c * fl_prim) + tot["path_vertices"] * fl_shade
+    fp32_nominal = 148 * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+    out["C3"] = {"workload": f"random spheres ({len(sh)} objects) 3840x2160 {spp}spp MIS (of the config's 4096 spp)", "n_gpus": world,
+                 "value": 3840 * 2160 * spp / ms / 1e3, "unit": "Msamples/s", "mrays_per_s": rays / ms / 1e3, "ms": ms,
+                 "kernel_launches": int(tot["kernel_launches"]), "lbvh_build_ms": sc.build_ms,
+                 "nodes_per_ray": cnt["nodes_visited"] / rays_c, "prim_tests_per_ray": cnt["prim_tests"] / rays_c,
+                 "roofline": {"bound": "fp32", "achieved": flops / ms / 1e9, "peak": fp32_nominal, "unit": "TFLOP/s", "frac": flops / ms / 1e9 / fp32_nominal,
+                              "peak_source": "nominal 148 SM x 128 lanes x 2 x max SM clock", "flops_per_unit": {"node_visit": fl_node, "prim_test": fl_prim, "vertex": fl_shade}}}
+    sc.close()
+
+    # ---- C4: 1,002,530-triangle heightfield at 1920x1080 (formulation B, LBVH walked through L1/L2): HBM roofline
+    sh, mt, cam = scenes.heightfield_scene(1920, 1080)
+    sc = api.Scene(ctx, sh, mt)
+    spp = args.c4_spp
+    ms, st = _frame(api, dist, torch, ctx, sc, cam, spp, rank, world, ext, dev)
+    tot = _sum_over_ranks(torch, dist, dev, world, st, keys)
+    msc, stc = _frame(api, dist, torch, ctx, sc, cam, max(world, 4), rank, world, ext, dev, reps=0, counters=True)
+    cnt = _sum_over_ranks(torch, dist, dev, world, stc, keys)
+    rays_c = max(cnt["rays_primary"] + cnt["rays_shadow"] + cnt["rays_scattered"], 1.0)
+    rays = tot["rays_primary"] + tot["rays_shadow"] + tot["rays_scattered"]
+    node_b, prim_b = 64.0, 48.0                      # SURVEY 8d: bytes per node visit / per triangle test
+    alg_bytes = rays * (cnt["nodes_visited"] / rays_c * node_b + cnt["prim_tests"] / rays_c * prim_b)
+    parity = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            import hashlib
+            from oracle import pyoracle as O
+            O.build()
+            got = sc.bvh()
+            ref = O.lbvh_build(sh)
+            h = lambda b: hashlib.sha256(b["nodes"].tobytes() + b["prims"].tobytes() + b["codes"].tobytes()).hexdigest()[:16]
+            _, _, cam64 = scenes.heightfield_scene(64, 64)
+            ids, t, _ = api.trace_primary(ctx, sc, cam64, api.render_params(traversal="bvh"))
+            rid, rt, _ = O.trace_primary(oracle_cam(O, cam64), sh, mt, precision="f32")
+            hit = rid >= 0
+            parity = {"lbvh_hash_gpu": h(got), "lbvh_hash_cpu_twin": h(ref), "lbvh_bit_exact": h(got) == h(ref),
+                      "sampled_primary_rays": int(ids.size), "id_mismatches_vs_fp32_oracle_brute_force": int((ids != rid).sum()),
+                      "t_bit_exact": bool(np.array_equal(t[hit].view(np.uint32), rt[hit].astype(np.float32).view(np.uint32)))}
+        except Exception as e:
+            parity = {"error": str(e)}
+    out["C4"] = {"workload": f"heightfield ({len(sh)} triangles) 1920x1080 {spp}spp MIS", "n_gpus": world,
+                 "value": 1920 * 1080 * spp / ms / 1e3, "unit": "Msamples/s", "mrays_per_s": rays / ms / 1e3, "ms": ms,
+                 "kernel_launches": int(tot["kernel_launches"]), "lbvh_build_ms": sc.build_ms, "lbvh_build_launches": sc.build_launches,
+                 "nodes_per_ray": cnt["nodes_visited"] / rays_c, "prim_tests_per_ray": cnt["prim_tests"] / rays_c,
+                 "roofline": {"bound": "hbm", "achieved": alg_bytes / ms / 1e6, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                              "frac": alg_bytes / ms / 1e6 / peaks["hbm_gbs"], "peak_source": peaks_src,
+                              "bytes_per_unit": {"node_visit": node_b, "prim_test": prim_b},
+                              "note": "algorithmic bytes = nodes visited x 64 + primitive tests x 48 from device counters (PT_FLAG_COUNTERS pass); "
+                                      "dram__bytes of the walk kernels: profiles/"},
+                 "parity": parity}
+    sc.close()
+
+    # ---- C5: convergence sweep points on the default scene at 1920x1080 (spp split over the ranks + one reduce each)
+    sh, mt, cam = scenes.default_scene(1920, 1080)
+    sc = api.Scene(ctx, sh, mt)
+    pts = []
+    for spp in (1, 16, 256, 4096):
+        ms, st = _frame(api, dist, torch, ctx, sc, cam, spp, rank, world, ext, dev, reps=2 if spp < 4096 else 1)
+        pts.append({"spp": spp, "ms": ms, "value": 1920 * 1080 * spp / ms / 1e3, "unit": "Msamples/s"})
+    out["C5"] = {"workload": "default scene 1920x1080, spp sweep (render + reduce + resolve per frame)", "n_gpus": world, "points": pts}
+    sc.close()
+    return out
+
+
 # ------------------------------------------------------------------------------------------ reference arm
 def run_reference(args, rank):
     """The reference's own CPU implementation of the path, restated (oracle/: f64, brute-force hit_scene, literal
@@ -333,11 +463,17 @@ def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
                 O.render(oc, sh, mt, O.RenderParams(spp=1), "f64", recursive=True, nthreads=ncpu)
                 r = O.render(oc, sh, mt, O.RenderParams(spp=args.cpu_spp, sample_offset=7), "f64", recursive=True, nthreads=ncpu)
                 cpu_baseline = {"value": npix * args.cpu_spp / r["seconds"] / 1e6, "unit": "Msamples/s", "cores": ncpu,
-                                "kind": "port", "sample": f"{WIDTH}x{HEIGHT} at {args.cpu_spp} spp (of {SPP}); f64, brute-force scan, recursive MIS with re-trace, OpenMP dynamic per pixel",
+                                "kind": "port", "sample": f"{WIDTH}x{HEIGHT} at {args.cpu_spp} spp (of {SPP}); f64, brute-force scan, recursive MIS with re-trace, OpenMP dynamic per pixel; g++ -O3 -march=x86-64-v3 -ffp-contract=off",
                                 "seconds": r["seconds"]}
         except Exception as e:   # the oracle is a checker; the bench line survives without it
             roofline = {"bound": "fp32", "error": f"oracle unavailable: {e}", "peak": fp32_tf, "unit": "TFLOP/s"}
 
+    configs = None
+    if not args.no_configs:
+        try:
+            configs = other_configs(args, rank, world, ctx, ext, dev)
+        except Exception as e:           # the headline line survives a failing side configuration
+            configs = {"error": repr(e)}
     if rank == 0:
         st0 = dev_stats[0]
         line = {
@@ -347,6 +483,7 @@ def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
             "config": {"workload": WORKLOAD, "width": WIDTH, "height": HEIGHT, "spp": spp_total, "spp_per_gpu": spp_g, "strategy": "mis",
                        "parallelism": f"spp-split x{world} + 1 NCCL reduce(sum)", "path_pool": st0["path_pool"],
                        "formulation": "hbm-queue wavefront" if args.hbm_queues else "shared-memory wavefront (one persistent launch)",
+                       "scan_mode": st0.get("scan_mode"),
                        "l2": "explicit 256 MiB write between steps"},
             "mrays_per_s": rays / (ms_total * 1e-3) / 1e6, "rays_per_sample": rays / max(samples, 1),
             "gpu_launches": int(launches), "clocks": clocks,
@@ -354,7 +491,11 @@ def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
                     "what": "pt_scene_create(host arrays)+pt_render(host radiance+RGBA8 buffers)" if world == 1 else
                             "scene upload per rank + render + NCCL reduce + resolve + D2H on rank 0"},
             "roofline": roofline, "roofline_hbm": roofline_hbm, "kernel_ms": kernel_ms, "cpu_baseline": cpu_baseline,
+            "configs": configs,
         }
+        lib_override = os.environ.get("PT_LIB")
+        if lib_override:
+            line["config"]["lib_override"] = lib_override
         emit(line)
 
 
@@ -369,6 +510,9 @@ def main():
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU-baseline sample")
     ap.add_argument("--ref-spp", type=int, default=2, help="spp per step of the --impl reference arm")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C3 / C4 / C5 sub-records")
+    ap.add_argument("--c3-spp", type=int, default=64)
+    ap.add_argument("--c4-spp", type=int, default=16)
     ap.add_argument("--hbm-queues", action="store_true", help="force the HBM-queue wavefront (one launch per stage per bounce)")
     ap.add_argument("--profile-in-timed", action="store_true", help="record per-kernel events inside the timed steps")
     args = ap.parse_args()
