@@ -155,7 +155,8 @@ int32_t pt_bvh_download(pt_context* ctx, const pt_scene* scene, uint32_t* codes_
                         float* bounds);
 uint32_t pt_scene_num_objects(const pt_scene* scene);
 uint32_t pt_scene_num_lights(const pt_scene* scene);
-/* Device time (CUDA events) pt_scene_create spent packing the scene and building the LBVH, and the kernels it launched. */
+/* Device time (CUDA events) of the LBVH build inside pt_scene_create — primitive boxes, Morton codes, radix sort, hierarchy,
+ * refit; allocation and the host-to-device copy of the scene are outside — and the kernels it launched. */
 float pt_scene_build_ms(const pt_scene* scene);
 uint32_t pt_scene_build_launches(const pt_scene* scene);
 

@@ -246,14 +246,12 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
         cudaMemcpyAsync(d_mats, materials, sizeof(pt_material) * n, cudaMemcpyHostToDevice, ctx->stream);
     }
     if (!lights.empty()) cudaMemcpyAsync(sc->dev.light_ids, lights.data(), 4 * lights.size(), cudaMemcpyHostToDevice, ctx->stream);
-    cudaEventRecord(ctx->ev[2], ctx->stream);
     int rc = scene_pack_launch(ctx, d_shapes, d_mats, n, sc->dev);
     if (rc) return cleanup(rc);
-    uint64_t launches = n ? (sc->dev.n_brute ? 2 : 1) : 0;
-    rc = lbvh_build_device(ctx, d_shapes, n, sc->dev, &launches);
+    uint64_t launches = 0;
+    rc = lbvh_build_device(ctx, d_shapes, n, sc->dev, &launches);   // records ev[2] / ev[3] around its kernels and synchronises
     if (rc) return cleanup(rc);
-    cudaEventRecord(ctx->ev[3], ctx->stream);
-    if (cudaEventSynchronize(ctx->ev[3]) == cudaSuccess) cudaEventElapsedTime(&sc->build_ms, ctx->ev[2], ctx->ev[3]);
+    cudaEventElapsedTime(&sc->build_ms, ctx->ev[2], ctx->ev[3]);
     sc->build_launches = (uint32_t)launches;
     cleanup(0);
     *out = sc;
