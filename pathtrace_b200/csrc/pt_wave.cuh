@@ -302,6 +302,7 @@ PT_DEV void closest_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, fl
             if (hr && cr < 0) { test(~cr); hr = false; }
             if (hl && hr) {
                 if (tr < tl) { int t = cl; cl = cr; cr = t; }
+                PT_CHECK(sp < kStackDepth);
                 stack[sp++] = cr; node = cl;
             } else if (hl) node = cl;
             else if (hr) node = cr;
@@ -350,7 +351,7 @@ PT_DEV bool any_hit(const G& g, uint32_t n_objects, float3 ro, float3 rd, float 
             if (hit_prim(q0, q1, q2, ro, rd, t_min, t_max) >= 0.0f) return true;
             hr = false;
         }
-        if (hl && hr) { stack[sp++] = cr; node = cl; }
+        if (hl && hr) { PT_CHECK(sp < kStackDepth); stack[sp++] = cr; node = cl; }
         else if (hl) node = cl;
         else if (hr) node = cr;
         else { if (sp == 0) return false; node = stack[--sp]; }
@@ -423,6 +424,7 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish, unsign
             const bool hr = slab(v3(c), v3(d), ro, inv, t_min, tmax, tr);
             if (hl && hr) {
                 const bool swap = tr < tl;
+                PT_CHECK(sp < kStackDepth);
                 stack[sp++] = swap ? cl : cr;
                 node = swap ? cr : cl;
             } else if (hl) node = cl;
@@ -519,6 +521,7 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
     if (h.y == 0xffffffffu) { o.finished = true; return o; }   // background is black, rendering.rs:140-141
     const float3 ro = v3(ro4), rd = v3(rd4);
     const int obj = (int)h.y;
+    PT_CHECK(obj >= 0);
     const float t = __uint_as_float(h.x);
     float4 q0, q1, q2, q3;
     sc.prim(obj, q0, q1, q2, q3);
@@ -556,6 +559,7 @@ PT_DEV VertexOut shade_vertex(const Scene& sc, const Frame& f, bool mis, float4 
     if (mis && sc.n_lights > 0) {
         uint32_t lw = (b0.x & 0xffu) | ((b0.y & 0xffu) << 8) | ((b0.z & 0xffu) << 16) | ((b0.w & 0xffu) << 24);
         uint32_t li = sc.light(urange(lw, sc.n_lights));
+        PT_CHECK(urange(lw, sc.n_lights) < sc.n_lights);
         float4 l0, l1, l2, l3;
         sc.prim((int)li, l0, l1, l2, l3);
         float3 le = sc.emission((int)li);

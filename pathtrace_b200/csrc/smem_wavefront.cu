@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             const bool cont = e < n_cont, seed = e >= kSwSlots - n_new;
             if (cont || seed) {
                 j = s_list[e];
+                PT_CHECK(j < (uint32_t)kSwSlots);
                 float4 ro, rd;
                 if (seed) {
                     uint2 m;
@@ -220,6 +221,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                 }
                 float t; int id;
                 trace_closest(v3(ro), v3(rd), seed, t, id);
+                PT_CHECK(id < (int)s.n_objects);
                 s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
                 if (id < 0) c = CLS_MISS;
                 else {
@@ -235,6 +237,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             if (rank == 0 && c != CLS_DEAD) pos = atom_add_shared(&s_cls[par][c], (uint32_t)__popc(same));
             pos = __shfl_sync(0xffffffffu, pos, __ffs(same) - 1) + rank;
             if (c != CLS_DEAD) {
+                PT_CHECK(pos < (uint32_t)kSwSlots);
                 uint16_t* ord = (c == CLS_MIRROR || c == CLS_DIFFUSE) ? s_ord_a : s_ord_b;
                 ord[(c == CLS_MIRROR || c == CLS_EMISSIVE) ? pos : kSwSlots - 1 - pos] = (uint16_t)j;
             }
@@ -256,6 +259,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             else                { idx = (tile - i2) * 32 + lane; cnt = n_mis; ord = s_ord_b; fwd = false; }
             const bool alive = idx < cnt;
             const uint32_t j = alive ? ord[fwd ? idx : kSwSlots - 1 - idx] : 0u;
+            PT_CHECK(j < (uint32_t)kSwSlots && n_mir + n_dif <= (uint32_t)kSwSlots && n_emi + n_mis <= (uint32_t)kSwSlots);
             const uint2 meta = s_meta[j];
             bool finished = false, emit_shadow = false;
             float3 sh_d = v3(0.f, 0.f, 0.f), sh_c = v3(0.f, 0.f, 0.f), p_hit = v3(0.f, 0.f, 0.f);
@@ -287,6 +291,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                 // one atomic for both ends of the list: continuing count in the low half, re-seed count in the high half
                 const uint32_t b = warp_atom_add_shared(&s_len[par ^ 1], (uint32_t)__popc(con) | ((uint32_t)__popc(fin) << 16));
                 const uint32_t bfin = b >> 16, bcon = b & 0xffffu;
+                PT_CHECK(bfin + bcon + __popc(fin) + __popc(con) <= (uint32_t)kSwSlots);
                 if (alive) s_list[finished ? kSwSlots - 1 - (bfin + __popc(fin & lt_mask)) : bcon + __popc(con & lt_mask)] = (uint16_t)j;
             }
         }

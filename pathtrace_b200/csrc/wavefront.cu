@@ -317,6 +317,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool poo
         tile = __shfl_sync(0xffffffffu, tile, 0);
         if (tile >= NTILES) break;
         const uint32_t j = s_order[tile * 32 + lane];
+        PT_CHECK(j < (uint32_t)kShadeSlots);
         const uint32_t i = base + j;
         const uint2 meta = s_meta[j];
         bool alive = META_ALIVE(meta);
@@ -355,6 +356,7 @@ __global__ void __launch_bounds__(kShadeBlock, kShadeMinBlocks) k_shade(Pool poo
             sbase = __shfl_sync(0xffffffffu, sbase, 0);
             if (emit_shadow) {
                 uint32_t sidx = base + sbase + __popc(bal & ((1u << lane) - 1));
+                PT_CHECK(sidx < pool.P && sbase + __popc(bal) <= (uint32_t)kShadeSlots);
                 pool.sh_o[sidx] = make_float4(sh_o.x, sh_o.y, sh_o.z, sh_tmax);
                 pool.sh_d[sidx] = make_float4(sh_d.x, sh_d.y, sh_d.z, __uint_as_float(META_PIXEL(meta)));
                 pool.sh_c[sidx] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
