@@ -414,6 +414,9 @@ def _bench_ours(args, rank, world, local_rank, ctx, scene, sh, mt, cam):
             with torch.cuda.stream(ext):
                 accum.zero_()
                 prof_stats = [api.render_accumulate_device(ctx, scene, cam, pp, accum.data_ptr())]
+                # per-phase cycle shares come from the instrumented kernel variant in a pass of its own
+                pc = api.render_params(spp=max(spp_g // 8, 1), sample_offset=off_g, path_pool=args.pool, phase_clocks=True, hbm_queues=args.hbm_queues)
+                prof_stats[0]["phase_share"] = api.render_accumulate_device(ctx, scene, cam, pc, accum.data_ptr())["phase_share"]
         kernel_ms = {k: sum(s["ms_kernel"][k] for s in prof_stats) for k in api.KERNEL_CLASSES}
         n_kernel = {k: sum(s["n_kernel"][k] for s in prof_stats) for k in api.KERNEL_CLASSES}
         fp32_tf, _ = api.measure_fp32_peak(ctx)

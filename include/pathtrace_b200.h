@@ -78,9 +78,11 @@ typedef struct {
     uint32_t path_pool;        /* wavefront pool size in paths; 0 = default */
 } pt_render_params;
 enum {
-    PT_FLAG_PROFILE = 1,     /* time every kernel launch with CUDA events into pt_stats.ms_kernel (slower) */
+    PT_FLAG_PROFILE = 1,     /* time every kernel launch with CUDA events into pt_stats.ms_kernel (the kernels themselves are unchanged) */
     PT_FLAG_HBM_QUEUES = 2,  /* force the HBM-queue wavefront (one launch per stage per bounce) even when the scene is small
                                 enough for the shared-memory wavefront (one persistent launch per frame) */
+    PT_FLAG_PHASE_CLOCKS = 8,/* shared-memory wavefront: run the kernel variant that reads the cycle counter around its phases and fill
+                                pt_stats.phase_share (a few percent slower; implies the events of PT_FLAG_PROFILE) */
     PT_FLAG_COUNTERS = 4     /* count LBVH node visits and primitive tests into the stats of the HBM-queue wavefront (slower) */
 };
 enum { PT_K_GENERATE = 0, PT_K_TRACE_CLOSEST = 1, PT_K_SHADE = 2, PT_K_TRACE_SHADOW = 3, PT_K_SMEM_WAVEFRONT = 4, PT_K_COUNT = 5 };
@@ -98,7 +100,7 @@ typedef struct {
     float ms_kernel[5];         /* PT_FLAG_PROFILE only: summed CUDA-event time per kernel class (PT_K_*) */
     uint32_t n_kernel[5];       /* launches per kernel class */
     uint32_t path_pool;         /* pool size actually used */
-    float phase_share[3];       /* PT_FLAG_PROFILE, shared-memory wavefront: share of warp cycles in closest-hit items, shading (+ shadow ray) items, waiting */
+    float phase_share[3];       /* PT_FLAG_PHASE_CLOCKS, shared-memory wavefront: share of warp cycles in closest-hit items, shading (+ shadow ray) items, waiting */
     uint32_t scan_mode;         /* shared-memory wavefront: 0 LBVH, 1 scan table, 2 constant-bank scan (checked), 3 constant-bank scan (in-domain),
                                    4 = 3 for primary rays + precomputed-transform test for shadow and scattered rays; 0xffffffff otherwise */
 } pt_stats;

@@ -117,10 +117,10 @@ def camera_struct(cam: Camera) -> pt_camera:
 
 
 def render_params(spp=3000, sample_offset=0, min_depth=4, max_depth=50, strategy="mis", traversal="auto", seed=0x5EED,
-                  t_min=1e-3, path_pool=0, profile=False, hbm_queues=False, counters=False, n_light_samples=1) -> pt_render_params:
+                  t_min=1e-3, path_pool=0, profile=False, hbm_queues=False, counters=False, n_light_samples=1, phase_clocks=False) -> pt_render_params:
     s = STRATEGY[strategy] if isinstance(strategy, str) else int(strategy)
     t = TRAVERSAL[traversal] if isinstance(traversal, str) else int(traversal)
-    flags = (1 if profile else 0) | (2 if hbm_queues else 0) | (4 if counters else 0)
+    flags = (1 if profile else 0) | (2 if hbm_queues else 0) | (4 if counters else 0) | (8 if phase_clocks else 0)
     return pt_render_params(spp, sample_offset, min_depth, max_depth, n_light_samples, s, t, flags, seed, t_min, path_pool)
 
 

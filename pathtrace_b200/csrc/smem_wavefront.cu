@@ -333,7 +333,8 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
     if (f.total_work == 0) { if (stats) stats->samples = 0; return PT_OK; }
     f.blo = make_float3(scene.bounds[0], scene.bounds[1], scene.bounds[2]);
     f.bhi = make_float3(scene.bounds[3], scene.bounds[4], scene.bounds[5]);
-    const bool profile = (rl.prm.flags & PT_FLAG_PROFILE) != 0;
+    const bool profile = (rl.prm.flags & (PT_FLAG_PROFILE | PT_FLAG_PHASE_CLOCKS)) != 0;   // CUDA events around the launch
+    const bool phases = (rl.prm.flags & PT_FLAG_PHASE_CLOCKS) != 0;                           // the kernel variant that reads clock64 per phase
     const size_t smem = sw_smem_bytes(scene.n_objects, scene.n_nodes, scene.n_lights, brute);
 
     auto pick = [&](auto kernel, int& occ) -> int {
@@ -347,7 +348,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
     const uint32_t n_fast_pairs = scene.n_fast_pairs;
     int occ = 0, rc;
     auto with_kernel = [&](auto&& fn) -> int {
-        switch (mode * 2 + (profile ? 1 : 0)) {
+        switch (mode * 2 + (phases ? 1 : 0)) {
             case 0: return fn(k_smem_wavefront<0, false>);
             case 1: return fn(k_smem_wavefront<0, true>);
             case 2: return fn(k_smem_wavefront<1, false>);
@@ -399,8 +400,8 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         std::vector<uint32_t> it(grid);
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(bs.data(), out.block_stats, 16 * (size_t)grid, cudaMemcpyDeviceToHost, st));
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(it.data(), out.block_iters, 4 * (size_t)grid, cudaMemcpyDeviceToHost, st));
-        std::vector<unsigned long long> clk(profile ? 3 * (size_t)grid : 0);
-        if (profile) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(clk.data(), out.block_clk, 24 * (size_t)grid, cudaMemcpyDeviceToHost, st));
+        std::vector<unsigned long long> clk(phases ? 3 * (size_t)grid : 0);
+        if (phases) PT_CUDA_CHECK(ctx, cudaMemcpyAsync(clk.data(), out.block_clk, 24 * (size_t)grid, cudaMemcpyDeviceToHost, st));
         PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
         uint64_t a = 0, b = 0, c = 0, d = 0, itmax = 0;
         for (auto& v : bs) { a += v.x; b += v.y; c += v.z; d += v.w; }
@@ -415,7 +416,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
             cudaEventElapsedTime(&ms, ctx->prof_events[0], ctx->prof_events[1]);
             stats->ms_kernel[PT_K_SMEM_WAVEFRONT] = ms;
             double t = 0, sh = 0, h = 0;
-            for (size_t k = 0; k < grid; ++k) { t += (double)clk[3 * k]; sh += (double)clk[3 * k + 1]; h += (double)clk[3 * k + 2]; }
+            for (size_t k = 0; phases && k < grid; ++k) { t += (double)clk[3 * k]; sh += (double)clk[3 * k + 1]; h += (double)clk[3 * k + 2]; }
             double tot = t + sh + h;
             if (tot > 0) { stats->phase_share[0] = (float)(t / tot); stats->phase_share[1] = (float)(sh / tot); stats->phase_share[2] = (float)(h / tot); }
         }

@@ -31,6 +31,7 @@ pub const PT_TRAVERSAL_BRUTE_FAST: u32 = 6;
 pub const PT_FLAG_PROFILE: u32 = 1;
 pub const PT_FLAG_HBM_QUEUES: u32 = 2;
 pub const PT_FLAG_COUNTERS: u32 = 4;
+pub const PT_FLAG_PHASE_CLOCKS: u32 = 8;
 
 /// `SphereShape{center, radius}` (shape.rs:38-43): kind 0, v = [cx, cy, cz, r, ..]; `TriangleShape{v0, v1, v2}`
 /// (shape.rs:148-152): kind 1, v = [v0.xyz, v1.xyz, v2.xyz].
