@@ -146,6 +146,23 @@ int32_t pt_resolve_device(pt_context* ctx, const void* d_accum_f4, uint32_t widt
 void* pt_context_stream(pt_context* ctx);
 int32_t pt_context_synchronize(pt_context* ctx);
 
+/* pt_render for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  The same samples and the same
+ * kernels as pt_render, but the scratch memory (the float4 sum buffer of the frame and the kernel's work counter / per-CTA
+ * statistics) is a static device array inside the library instead of context-owned cudaMalloc'd buffers, and the results are
+ * written to the CALLER's device buffers d_radiance_rgb (W*H*3 floats) and d_rgba8 (W*H*4 bytes); either may be null.  The
+ * call makes no cudaMalloc / cudaFree / event creation; it enqueues on pt_context_stream and returns without waiting
+ * (pt_context_synchronize, or order later work on that stream).
+ * Limits (PT_ERR_INVALID with a message otherwise): width * height <= PT_NOALLOC_MAX_PIXELS; p->flags == 0; a scene the
+ * shared-memory wavefront serves (up to 1024 objects staged in shared memory; larger scenes need HBM path queues); at most
+ * 1024 CTAs (only an explicit p->path_pool can ask for more).
+ * The array (PT_NOALLOC_MAX_PIXELS * 16 B + 48 KiB, about 1.05 MiB) is held by every GPU that loads the library until the
+ * process exits; all calls on a device share it, it is cleared at the start of each call, and two calls that overlap on the
+ * GPU (two contexts of one device, or one context driven from two threads) race on it. */
+#define PT_NOALLOC_MAX_PIXELS 65536u
+int32_t pt_render_device_noalloc(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p,
+                                 void* d_radiance_rgb, void* d_rgba8);
+
 /* Parity hooks.
  * pt_trace_primary: closest hit of one primary ray per pixel.  jitter==0: fixed offsets (ox, oy) (camera.rs:139-147);
  * jitter!=0: the offsets of sample `sample` from the render RNG.  obj_id: W*H int32 (-1 = miss); t: W*H floats (+inf = miss);

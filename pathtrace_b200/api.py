@@ -61,7 +61,7 @@ EXPORTS = ["pt_context_create", "pt_context_destroy", "pt_last_error", "pt_scene
            "pt_trace_primary", "pt_bvh_download", "pt_scene_num_objects", "pt_scene_num_lights", "pt_scene_build_ms",
            "pt_scene_build_launches", "pt_export_luminance", "pt_write_ppm", "pt_version", "pt_measure_fp32_peak",
            "pt_group_create", "pt_group_destroy", "pt_group_size", "pt_group_context", "pt_group_last_error",
-           "pt_group_scene_create", "pt_group_scene_destroy", "pt_group_render"]
+           "pt_group_scene_create", "pt_group_scene_destroy", "pt_group_render", "pt_render_device_noalloc"]
 
 _lib = None
 
@@ -247,6 +247,17 @@ def render_accumulate_device(ctx: Context, scene: Scene, cam: Camera, params: pt
 def resolve_device(ctx: Context, d_accum_ptr: int, width: int, height: int, total_spp: int, d_radiance_ptr: int = 0, d_rgba_ptr: int = 0):
     ctx.check(ctx.lib.pt_resolve_device(ctx.handle, C.c_void_p(d_accum_ptr), C.c_uint32(width), C.c_uint32(height), C.c_uint32(total_spp),
                                         C.c_void_p(d_radiance_ptr or None), C.c_void_p(d_rgba_ptr or None)), "pt_resolve_device")
+
+
+NOALLOC_MAX_PIXELS = 65536       # PT_NOALLOC_MAX_PIXELS
+
+
+def render_device_noalloc(ctx: Context, scene: Scene, cam: Camera, params: pt_render_params, d_radiance_ptr: int = 0, d_rgba_ptr: int = 0):
+    """pt_render_device_noalloc: renders into the caller's device buffers with the library's static scratch array (no
+    cudaMalloc on the path); enqueued on ctx.stream, not waited for."""
+    c = camera_struct(cam)
+    ctx.check(ctx.lib.pt_render_device_noalloc(ctx.handle, scene.handle, C.byref(c), C.byref(params), C.c_void_p(d_radiance_ptr or None),
+                                               C.c_void_p(d_rgba_ptr or None)), "pt_render_device_noalloc")
 
 
 def trace_primary(ctx: Context, scene: Scene, cam: Camera, params: pt_render_params = None, jitter=False, ox=0.5, oy=0.5, sample=0,

@@ -325,6 +325,19 @@ int32_t pt_render(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, 
     return PT_OK;
 }
 
+// No counterpart in the reference: see include/pathtrace_b200.h and the
+// scratch array in smem_wavefront.cu.
+int32_t pt_render_device_noalloc(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, void* d_radiance,
+                                 void* d_rgba) {
+    if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_render_device_noalloc: null argument");
+    if (!d_radiance && !d_rgba) return fail(ctx, PT_ERR_INVALID, "pt_render_device_noalloc: both output pointers are null");
+    if (!valid_camera(cam)) return fail(ctx, PT_ERR_INVALID, "pt_render_device_noalloc: bad camera (width/height must be >= 2)");
+    if (!valid_params(p) || p->spp == 0) return fail(ctx, PT_ERR_INVALID, std::string("pt_render_device_noalloc: spp must be > 0; ") + kBadParams);
+    if (scene->ctx != ctx) return fail(ctx, PT_ERR_INVALID, "pt_render_device_noalloc: scene belongs to another context");
+    cudaSetDevice(ctx->device);
+    return keep(ctx, smem_wavefront_render_noalloc(ctx, scene->dev, *cam, *p, static_cast<float*>(d_radiance), static_cast<uint8_t*>(d_rgba)));
+}
+
 int32_t pt_render_moments(pt_context* ctx, const pt_scene* scene, const pt_camera* cam, const pt_render_params* p, uint32_t batches,
                           float* radiance, float* moment2, pt_stats* stats) {
     if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_render_moments: null argument");

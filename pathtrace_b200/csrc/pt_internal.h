@@ -93,6 +93,9 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats);
 // smem_wavefront.cu
 bool smem_wavefront_applicable(const pt_context* ctx, const SceneDev& scene, bool brute);
 int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, pt_stats* stats);
+// the shared-memory wavefront with its scratch in a file-scope device array (pt_render_device_noalloc)
+int smem_wavefront_render_noalloc(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm,
+                                  float* d_radiance, uint8_t* d_rgba);
 int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
                             float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches);
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba);

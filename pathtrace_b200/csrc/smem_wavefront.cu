@@ -28,6 +28,8 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <string>
 #include <vector>
 
 #include "pt_wave.cuh"
@@ -422,4 +424,114 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         }
     }
     return PT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// pt_render_device_noalloc: the same kernel with its scratch memory in a file-scope device array instead of cudaMalloc'd
+// buffers (no counterpart in the reference; added for callers that cannot allocate:
+// code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+//
+// Scratch of one call = the float4 accumulation buffer of the frame (what pt_render keeps in pt_context::d_accum) followed by
+// the kernel's SwOut block (per-CTA statistics and the work hand-out counter, pt_context::pool_mem in pt_render).  The array is
+// part of the module image: every GPU that loads the library holds kNoAllocScratchBytes of it until the process exits.  All
+// calls on a device share it and it keeps the last call's contents, so the accumulation buffer and the work counter are
+// cleared at the start of every call; two calls that overlap on the GPU (two contexts on one device, or one context used from
+// two threads) race on it.
+constexpr uint32_t kNoAllocMaxPixels = PT_NOALLOC_MAX_PIXELS;                 // 65536 pixels -> 1 MiB of float4 sums
+constexpr uint32_t kNoAllocMaxGrid = 1024;                                    // CTAs (148 x occupancy on a B200; path_pool may ask for more)
+constexpr size_t kNoAllocAccumBytes = sizeof(float4) * (size_t)kNoAllocMaxPixels;
+constexpr size_t kNoAllocOutBytes = (((16 + 4 + 24) * (size_t)kNoAllocMaxGrid + 255) & ~size_t(255)) + 256;
+constexpr size_t kNoAllocScratchBytes = kNoAllocAccumBytes + kNoAllocOutBytes;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoAllocMaxDevices] = {};   // device address of g_noalloc_scratch per device ordinal (the name itself is a host-side stand-in)
+
+// Device address of the scratch array on ctx->device, looked up once per device with that device current.
+int noalloc_scratch(pt_context* ctx, unsigned char** out) {
+    if (ctx->device < 0 || ctx->device >= kNoAllocMaxDevices) { ctx->err = "pt_render_device_noalloc: device ordinal beyond 63"; return PT_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[ctx->device]) {
+        PT_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+        void* p = nullptr;
+        PT_CUDA_CHECK(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) { ctx->err = "pt_render_device_noalloc: cudaGetSymbolAddress returned a null address"; return PT_ERR_CUDA; }
+        g_noalloc_ptr[ctx->device] = p;
+    }
+    *out = static_cast<unsigned char*>(g_noalloc_ptr[ctx->device]);
+    return PT_OK;
+}
+}  // namespace
+
+// Enqueues clear -> k_smem_wavefront -> k_resolve on the context's stream; no cudaMalloc / cudaFree / event creation on this path.
+int smem_wavefront_render_noalloc(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm,
+                                  float* d_radiance, uint8_t* d_rgba) {
+    cudaStream_t st = ctx->stream;
+    const uint64_t npix = (uint64_t)cam.width * cam.height;
+    if (npix > kNoAllocMaxPixels) {
+        ctx->err = "pt_render_device_noalloc: frame of " + std::to_string(npix) + " pixels exceeds the static scratch (PT_NOALLOC_MAX_PIXELS = " +
+                   std::to_string(kNoAllocMaxPixels) + "); use pt_render";
+        return PT_ERR_INVALID;
+    }
+    if (prm.flags != 0) { ctx->err = "pt_render_device_noalloc: flags must be 0 (profiling, counters and the HBM-queue formulation allocate)"; return PT_ERR_INVALID; }
+    // the traversal rule of pt_render (wavefront.cu: pick_mode)
+    const bool brute = prm.traversal >= PT_TRAVERSAL_BRUTE || (prm.traversal == PT_TRAVERSAL_AUTO && scene.n_objects <= 16) || scene.n_objects < 2;
+    if (!smem_wavefront_applicable(ctx, scene, brute)) {
+        ctx->err = "pt_render_device_noalloc: the scene does not fit the shared-memory wavefront (its HBM path queues need cudaMalloc); use pt_render";
+        return PT_ERR_INVALID;
+    }
+    unsigned char* scratch = nullptr;
+    int rc = noalloc_scratch(ctx, &scratch);
+    if (rc) return rc;
+    float4* d_accum = reinterpret_cast<float4*>(scratch);
+
+    SceneView sv = make_scene_view(scene);
+    Frame f = make_frame(cam, prm, d_accum);
+    if (f.total_work == 0) { ctx->err = "pt_render_device_noalloc: spp must be > 0"; return PT_ERR_INVALID; }
+    f.blo = make_float3(scene.bounds[0], scene.bounds[1], scene.bounds[2]);
+    f.bhi = make_float3(scene.bounds[3], scene.bounds[4], scene.bounds[5]);
+    f.chunk = 0;
+    const size_t smem = sw_smem_bytes(scene.n_objects, scene.n_nodes, scene.n_lights, brute);
+    const int mode = !brute ? 0 : pick_scan_mode(scene, cam, prm.traversal);
+    auto with_kernel = [&](auto&& fn) -> int {
+        switch (mode) {
+            case 0: return fn(k_smem_wavefront<0, false>);
+            case 1: return fn(k_smem_wavefront<1, false>);
+            case 2: return fn(k_smem_wavefront<2, false>);
+            case 3: return fn(k_smem_wavefront<3, false>);
+            default: return fn(k_smem_wavefront<4, false>);
+        }
+    };
+    int occ = 0;
+    rc = with_kernel([&](auto kernel) -> int {
+        PT_CUDA_CHECK(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kSwBlock, smem));
+        return PT_OK;
+    });
+    if (rc) return rc;
+    if (occ < 1) { ctx->err = "pt_render_device_noalloc: kernel does not fit on an SM"; return PT_ERR_CUDA; }
+    const uint64_t want = prm.path_pool ? ((uint64_t)prm.path_pool + kSwSlots - 1) / kSwSlots : (uint64_t)ctx->sm_count * occ;
+    const uint64_t need = (f.total_work + kSwSlots - 1) / kSwSlots;
+    uint64_t grid = want < need ? want : need;
+    if (grid == 0) grid = 1;
+    if (grid > kNoAllocMaxGrid) {
+        ctx->err = "pt_render_device_noalloc: " + std::to_string(grid) + " CTAs exceed the static scratch (" + std::to_string(kNoAllocMaxGrid) + "); lower path_pool";
+        return PT_ERR_INVALID;
+    }
+    SwOut out;
+    unsigned char* p = scratch + kNoAllocAccumBytes;
+    out.block_stats = reinterpret_cast<uint4*>(p);
+    out.block_clk = reinterpret_cast<unsigned long long*>(p + 16 * (size_t)grid);
+    out.block_iters = reinterpret_cast<uint32_t*>(p + (16 + 24) * (size_t)grid);
+    out.work_next = reinterpret_cast<unsigned long long*>(p + (((16 + 24 + 4) * (size_t)grid + 255) & ~size_t(255)));
+    // the array keeps the previous call's sums and counter: both must start at zero
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(d_accum, 0, sizeof(float4) * (size_t)npix, st));
+    PT_CUDA_CHECK(ctx, cudaMemsetAsync(out.work_next, 0, 8, st));
+    const FastParam fp = make_fast_param(scene);
+    const BruteParam bp = make_brute_param(scene);
+    with_kernel([&](auto kernel) { kernel<<<(uint32_t)grid, kSwBlock, smem, st>>>(sv, f, out, bp, fp, scene.n_fast_pairs, scene.n_fast_spheres); return PT_OK; });
+    PT_CUDA_CHECK(ctx, cudaGetLastError());
+    return resolve_launch(ctx, d_accum, cam.width, cam.height, prm.spp, d_radiance, d_rgba);
 }

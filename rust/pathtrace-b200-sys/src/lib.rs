@@ -32,6 +32,7 @@ pub const PT_FLAG_PROFILE: u32 = 1;
 pub const PT_FLAG_HBM_QUEUES: u32 = 2;
 pub const PT_FLAG_COUNTERS: u32 = 4;
 pub const PT_FLAG_PHASE_CLOCKS: u32 = 8;
+pub const PT_NOALLOC_MAX_PIXELS: u32 = 65536;
 
 /// `SphereShape{center, radius}` (shape.rs:38-43): kind 0, v = [cx, cy, cz, r, ..]; `TriangleShape{v0, v1, v2}`
 /// (shape.rs:148-152): kind 1, v = [v0.xyz, v1.xyz, v2.xyz].
@@ -143,6 +144,11 @@ extern "C" {
                                        p: *const pt_render_params, d_accum_f4: *mut c_void, stats_or_null: *mut pt_stats) -> i32;
     pub fn pt_resolve_device(ctx: *mut pt_context, d_accum_f4: *const c_void, width: u32, height: u32, total_spp: u32,
                              d_radiance_rgb: *mut c_void, d_rgba8: *mut c_void) -> i32;
+
+    /// No counterpart in the reference: `pt_render` into the caller's device buffers with the library's static scratch array
+    /// (no cudaMalloc on the path); `width * height <= PT_NOALLOC_MAX_PIXELS`, `flags == 0`.
+    pub fn pt_render_device_noalloc(ctx: *mut pt_context, scene: *const pt_scene, cam: *const pt_camera, p: *const pt_render_params,
+                                    d_radiance_rgb: *mut c_void, d_rgba8: *mut c_void) -> i32;
 
     pub fn pt_trace_primary(ctx: *mut pt_context, scene: *const pt_scene, cam: *const pt_camera, p: *const pt_render_params,
                             jitter: i32, ox: f32, oy: f32, sample: u32, obj_id: *mut i32, t: *mut f32, dir_or_null: *mut f32) -> i32;

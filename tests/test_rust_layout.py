@@ -73,6 +73,7 @@ def test_extern_block_declares_every_export():
 
 def test_constants_match_header_enums():
     enums = dict((k, int(v)) for k, v in re.findall(r"\b(PT_[A-Z0-9_]+)\s*=\s*(\d+)", HEADER_NC))
+    enums.update((k, int(v)) for k, v in re.findall(r"#define\s+(PT_[A-Z0-9_]+)\s+(\d+)u?\b", HEADER_NC))
     consts = dict((k, int(v)) for k, v in re.findall(r"pub const (PT_[A-Z0-9_]+):\s*\w+\s*=\s*(\d+);", RUST_NC))
     assert consts, "no constants parsed"
     for k, v in consts.items():
