@@ -229,6 +229,7 @@ int32_t pt_scene_create(pt_context* ctx, const pt_shape* shapes, const pt_materi
             pairs += pair; i += pair ? 2 : 1;
         }
         sc->dev.n_brute = e; sc->dev.n_pairs = pairs;
+        sc->dev.shapes_host.assign(shapes, shapes + n);
     }
     if (sc->dev.n_brute && sc->dev.fp32_domain) build_fast_table(shapes, n, sc->dev);
     pt_shape* d_shapes = nullptr;

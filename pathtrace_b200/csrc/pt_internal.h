@@ -26,6 +26,7 @@ struct SceneDev {
     // triangle test can overflow, and every determinant is either below the 1e-8 rejection threshold or a normal number far
     // from 2^126 — the precondition of the unchecked pair test (pt_math.cuh: prcp_rn<false>, hit_triangle2<false, .>).
     bool fp32_domain = false;
+    std::vector<pt_shape> shapes_host;   // the caller's shapes for scenes with a scan table (<= 1024 objects): the primary-ray cull projects them per camera
     std::vector<float4> brute_host;      // host copy of the pair entries that fit a kernel parameter (pt_wave.cuh: BruteParam)
     // Secondary-ray scan (pt_wave.cuh: fast_pair): every triangle of the scene as a planar entry with its world -> (u, v, w)
     // affine map; two consecutive triangles that form a parallelogram share ONE entry.  8 float4 per pair of entries; empty

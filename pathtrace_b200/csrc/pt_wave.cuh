@@ -28,6 +28,7 @@ struct Frame {
     float t_min;
     float4* accum;           // per pixel: sum r, g, b, (reserved)
     float3 blo, bhi;         // padded scene bounds (SceneDev::bounds); blo.x > bhi.x: none
+    uint64_t magic_npix, magic_width;   // div_magic constants of npix and cam.width
 };
 
 struct SceneView {
@@ -40,15 +41,36 @@ struct SceneView {
     uint32_t n_brute, n_pairs;
 };
 
-PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
+// n / d for any 32-bit n with the host's m = floor(2^64 / d) + 1 (d >= 2): exact, because n * (m * d - 2^64) < 2^64.
+PT_DEV uint32_t div_magic(uint32_t n, uint64_t m) { return (uint32_t)__umul64hi((uint64_t)n, m); }
+inline uint64_t magic_of(uint32_t d) { return d >= 2 ? ~0ull / d + 1ull : 0ull; }   // (for a power of two this is 2^64 / d itself: exact as well)
+// Camera ray of work item (sample_rel, p): p = pixel index plus a small offset, p / npix further samples (the shared-memory
+// wavefront hands out contiguous ranges and decodes them without 64-bit division).
+PT_DEV void make_primary_at(const Frame& f, uint32_t sample_rel, uint32_t p, float4& ro, float4& rd, uint2& meta, uint32_t& px, uint32_t& py_flipped) {
+    const uint32_t q = div_magic(p, f.magic_npix);
+    const uint32_t pixel = p - q * f.npix, sample = f.sample_offset + sample_rel + q;
+    const uint32_t y = div_magic(pixel, f.magic_width), x = pixel - y * f.cam.width;
+    uint4 r = rng_block(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
+    px = x; py_flipped = f.cam.height - 1 - y;
+    float3 d = camera_dir(f.cam, x, py_flipped, u01(r.x), u01(r.y));             // world.rs:299
+    ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
+    rd = make_float4(d.x, d.y, d.z, 0.0f);
+    meta = make_uint2(pixel | 0x80000000u, sample & 0x00ffffffu);
+}
+PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta, uint32_t& px, uint32_t& py_flipped) {
     uint32_t sample = f.sample_offset + (uint32_t)(w / f.npix);
     uint32_t pixel = (uint32_t)(w % f.npix);
     uint32_t x = pixel % f.cam.width, y = pixel / f.cam.width;
     uint4 r = rng_block(pixel, sample, 0xFFFFFFFFu, 0u, f.k0, f.k1);
-    float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, u01(r.x), u01(r.y));   // world.rs:299
+    px = x; py_flipped = f.cam.height - 1 - y;
+    float3 d = camera_dir(f.cam, x, py_flipped, u01(r.x), u01(r.y));             // world.rs:299
     ro = make_float4(f.cam.origin.x, f.cam.origin.y, f.cam.origin.z, 1.0f);      // eta_ratio = 1, camera.rs:14
     rd = make_float4(d.x, d.y, d.z, 0.0f);
     meta = make_uint2(pixel | 0x80000000u, sample & 0x00ffffffu);
+}
+PT_DEV void make_primary(const Frame& f, uint64_t w, float4& ro, float4& rd, uint2& meta) {
+    uint32_t px, py;
+    make_primary(f, w, ro, rd, meta, px, py);
 }
 
 // ------------------------------------------------------------------------------------ traversal
@@ -153,6 +175,36 @@ PT_DEV void closest_hit_param(const BruteParam& bp, const G& g, float3 ro, float
 #undef PT_STEP
     for (uint32_t e = g.n_pairs; e < g.n_brute; ++e)
         single_closest(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 4], ro, rd, t_min, tmax, best_id);
+    if (best_id >= 0) best_t = tmax;
+}
+// Screen-space cull of the primary-ray scan.  Every camera ray of pixel (x, y_flipped) passes through the image-plane cell
+// [x, x+1] x [y_flipped, y_flipped+1] (camera.rs:139-147 with the jitter in (0, 1)), so a pair of triangles (or a sphere) whose
+// projection lies outside that cell cannot be hit: the host projects each entry in f64 (make_cull_param below) and stores a
+// padded pixel rectangle; a warp skips an entry when none of its lanes' pixels is inside.  Lanes that run the test anyway get
+// the exact answer, so ids and t are those of the full scan bit for bit (tested through pt_trace_primary).  Entries the host
+// cannot bound (a vertex behind the camera, a plane seen edge-on, the camera inside a sphere) keep the full-screen rectangle.
+constexpr int kCullSingles = 8;
+struct CullParam {
+    int4 pair[kParamPairs];        // (x0, y0, x1 - x0, y1 - y0) in the slot order of BruteParam; empty: x0 = INT_MAX
+    int4 single[kCullSingles];     // the first unpaired entries of the scan table, in table order
+    uint32_t enabled;              // host-side note; 0: every rectangle is the full screen (e.g. the caller's ray offsets are not in [0, 1])
+};
+PT_DEV bool cull_inside(int4 c, uint32_t x, uint32_t y) { return ((x - (uint32_t)c.x) <= (uint32_t)c.z) & ((y - (uint32_t)c.y) <= (uint32_t)c.w); }
+template <bool CHECKED, class G>
+PT_DEV void closest_hit_param_culled(const BruteParam& bp, const CullParam& cull, const G& g, uint32_t x, uint32_t y, float3 ro, float3 rd, float t_min,
+                                     float& best_t, int& best_id) {
+    best_t = FLT_MAX; best_id = -1;
+    float tmax = __int_as_float(0x7f800000);
+#define PT_STEP(k)                                                                                                            \
+    if (__any_sync(__activemask(), cull_inside(cull.pair[k], x, y)))                                                          \
+        pair_closest<CHECKED>(bp.e[5 * (k)], bp.e[5 * (k) + 1], bp.e[5 * (k) + 2], bp.e[5 * (k) + 3], bp.e[5 * (k) + 4], ro, rd, t_min, tmax, best_id);
+    PT_PARAM_SCAN(g.n_pairs, PT_STEP)
+#undef PT_STEP
+    for (uint32_t e = g.n_pairs; e < g.n_brute; ++e) {
+        const uint32_t k = e - g.n_pairs;
+        if (k < (uint32_t)kCullSingles && !__any_sync(__activemask(), cull_inside(cull.single[k], x, y))) continue;
+        single_closest(g.brute[5 * e], g.brute[5 * e + 1], g.brute[5 * e + 2], g.brute[5 * e + 4], ro, rd, t_min, tmax, best_id);
+    }
     if (best_id >= 0) best_t = tmax;
 }
 template <bool CHECKED, class G>
@@ -648,6 +700,84 @@ inline BruteParam make_brute_param(const SceneDev& scene) {   // right-aligned: 
         memcpy(bp.e + 5 * ((size_t)kParamPairs - scene.n_pairs), scene.brute_host.data(), sizeof(float4) * 5 * (size_t)scene.n_pairs);
     return bp;
 }
+// Pixel rectangles of the primary-ray cull (closest_hit_param_culled).  A point P is seen through image-plane coordinates
+// (u, v) with P - O = s (A + u H + v V), A = lower_left_corner - O, s > 0; pixel x covers u (W - 1) in (x, x + 1).  The bounds
+// are computed in f64 from the same f32 camera and vertex values the device uses and padded by 2 pixels: the FP32 test can
+// accept a ray that misses the exact triangle by rounding, which is far below a pixel unless the plane is seen edge-on
+// (|cos| < 1e-2 between the plane and the line of sight: such entries are not culled).
+inline CullParam make_cull_param(const SceneDev& scene, const pt_camera& cam, bool enable) {
+    CullParam cp;
+    const int4 full = make_int4(0, 0, 0x7fffffff, 0x7fffffff), none = make_int4(0x7fffffff, 0x7fffffff, 0, 0);
+    for (auto& r : cp.pair) r = full;
+    for (auto& r : cp.single) r = full;
+    cp.enabled = 0;
+    const uint32_t n = scene.n_objects;
+    if (!enable || scene.shapes_host.size() != n || scene.n_pairs > (uint32_t)kParamPairs) return cp;
+    const double O[3] = {cam.origin[0], cam.origin[1], cam.origin[2]};
+    double M[3][3];   // columns H, V, A
+    for (int r = 0; r < 3; ++r) { M[r][0] = cam.horizontal[r]; M[r][1] = cam.vertical[r]; M[r][2] = (double)cam.lower_left_corner[r] - O[r]; }
+    const double det = M[0][0] * (M[1][1] * M[2][2] - M[1][2] * M[2][1]) - M[0][1] * (M[1][0] * M[2][2] - M[1][2] * M[2][0]) +
+                       M[0][2] * (M[1][0] * M[2][1] - M[1][1] * M[2][0]);
+    if (!(std::fabs(det) > 1e-300) || !std::isfinite(det)) return cp;
+    double inv[3][3];
+    inv[0][0] = (M[1][1] * M[2][2] - M[1][2] * M[2][1]) / det; inv[0][1] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) / det; inv[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) / det;
+    inv[1][0] = (M[1][2] * M[2][0] - M[1][0] * M[2][2]) / det; inv[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) / det; inv[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) / det;
+    inv[2][0] = (M[1][0] * M[2][1] - M[1][1] * M[2][0]) / det; inv[2][1] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) / det; inv[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) / det;
+    struct Rect { double x0 = 1e300, x1 = -1e300, y0 = 1e300, y1 = -1e300; bool ok = true; };
+    auto add_point = [&](Rect& rc, const double P[3]) {
+        const double d[3] = {P[0] - O[0], P[1] - O[1], P[2] - O[2]};
+        const double su = inv[0][0] * d[0] + inv[0][1] * d[1] + inv[0][2] * d[2], sv = inv[1][0] * d[0] + inv[1][1] * d[1] + inv[1][2] * d[2],
+                     sw = inv[2][0] * d[0] + inv[2][1] * d[1] + inv[2][2] * d[2];
+        if (!(sw > 1e-4) || !std::isfinite(su) || !std::isfinite(sv) || !std::isfinite(sw)) { rc.ok = false; return; }   // behind (or near) the camera plane
+        const double xf = su / sw * ((double)cam.width - 1.0), yf = sv / sw * ((double)cam.height - 1.0);
+        if (!(std::fabs(xf) < 1e9) || !(std::fabs(yf) < 1e9)) { rc.ok = false; return; }
+        rc.x0 = std::fmin(rc.x0, xf); rc.x1 = std::fmax(rc.x1, xf); rc.y0 = std::fmin(rc.y0, yf); rc.y1 = std::fmax(rc.y1, yf);
+    };
+    auto add_triangle = [&](Rect& rc, const pt_shape& sh) {
+        double Pv[3][3];
+        for (int v = 0; v < 3; ++v) for (int c = 0; c < 3; ++c) Pv[v][c] = sh.v[3 * v + c];
+        const double e1[3] = {Pv[1][0] - Pv[0][0], Pv[1][1] - Pv[0][1], Pv[1][2] - Pv[0][2]}, e2[3] = {Pv[2][0] - Pv[0][0], Pv[2][1] - Pv[0][1], Pv[2][2] - Pv[0][2]};
+        const double nn[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+        const double nl = std::sqrt(nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2]);
+        if (!(nl > 0.0) || !std::isfinite(nl)) { rc.ok = false; return; }
+        double far2 = 0.0;
+        for (int v = 0; v < 3; ++v) { double q = 0; for (int c = 0; c < 3; ++c) q += (Pv[v][c] - O[c]) * (Pv[v][c] - O[c]); far2 = std::fmax(far2, q); }
+        const double dist = std::fabs(nn[0] * (O[0] - Pv[0][0]) + nn[1] * (O[1] - Pv[0][1]) + nn[2] * (O[2] - Pv[0][2])) / nl;
+        if (!(dist >= 1e-2 * std::sqrt(far2))) { rc.ok = false; return; }                                        // seen edge-on
+        for (int v = 0; v < 3; ++v) add_point(rc, Pv[v]);
+    };
+    auto add_sphere = [&](Rect& rc, const pt_shape& sh) {
+        const double c[3] = {sh.v[0], sh.v[1], sh.v[2]}, r = std::fabs((double)sh.v[3]) * (1.0 + 1e-6);
+        double d2 = 0; for (int k = 0; k < 3; ++k) d2 += (O[k] - c[k]) * (O[k] - c[k]);
+        if (!(std::sqrt(d2) > r * 1.001 + 1e-30) || !std::isfinite(r)) { rc.ok = false; return; }                 // camera inside or on the sphere
+        for (int m = 0; m < 8; ++m) { const double P[3] = {c[0] + ((m & 1) ? r : -r), c[1] + ((m & 2) ? r : -r), c[2] + ((m & 4) ? r : -r)}; add_point(rc, P); }
+    };
+    auto to_int4 = [&](const Rect& rc) {
+        if (!rc.ok) return full;
+        const double pad = 2.0;
+        const double x0 = std::floor(rc.x0) - pad, x1 = std::floor(rc.x1) + pad, y0 = std::floor(rc.y0) - pad, y1 = std::floor(rc.y1) + pad;
+        const double W1 = (double)cam.width - 1.0, H1 = (double)cam.height - 1.0;
+        if (x1 < 0.0 || y1 < 0.0 || x0 > W1 || y0 > H1) return none;
+        const int ix0 = (int)std::fmax(x0, 0.0), ix1 = (int)std::fmin(x1, W1), iy0 = (int)std::fmax(y0, 0.0), iy1 = (int)std::fmin(y1, H1);
+        return make_int4(ix0, iy0, ix1 - ix0, iy1 - iy0);
+    };
+    uint32_t ep = 0, es = 0;
+    for (uint32_t i = 0; i < n;) {                       // the pairing rule of k_brute_table (lbvh.cu)
+        const bool pair = i + 1 < n && scene.shapes_host[i].kind == PT_SHAPE_TRIANGLE && scene.shapes_host[i + 1].kind == PT_SHAPE_TRIANGLE;
+        Rect rc;
+        if (pair) {
+            add_triangle(rc, scene.shapes_host[i]); add_triangle(rc, scene.shapes_host[i + 1]);
+            if (ep < scene.n_pairs) cp.pair[(size_t)kParamPairs - scene.n_pairs + ep] = to_int4(rc);
+            ++ep; i += 2;
+        } else {
+            if (scene.shapes_host[i].kind == PT_SHAPE_TRIANGLE) add_triangle(rc, scene.shapes_host[i]); else add_sphere(rc, scene.shapes_host[i]);
+            if (es < (uint32_t)kCullSingles) cp.single[es] = to_int4(rc);
+            ++es; i += 1;
+        }
+    }
+    cp.enabled = 1;
+    return cp;
+}
 inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* accum) {
     Frame f;
     f.cam.origin = make_float3(c.origin[0], c.origin[1], c.origin[2]);
@@ -656,6 +786,7 @@ inline Frame make_frame(const pt_camera& c, const pt_render_params& p, float4* a
     f.cam.vertical = make_float3(c.vertical[0], c.vertical[1], c.vertical[2]);
     f.cam.width = c.width; f.cam.height = c.height;
     f.npix = c.width * c.height;
+    f.magic_npix = magic_of(f.npix); f.magic_width = magic_of(c.width);
     f.total_work = (uint64_t)f.npix * p.spp;
     f.sample_offset = p.sample_offset; f.min_depth = p.min_depth; f.max_depth = p.max_depth; f.strategy = p.strategy;
     f.k0 = (uint32_t)p.seed; f.k1 = (uint32_t)(p.seed >> 32);

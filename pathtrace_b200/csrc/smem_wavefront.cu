@@ -100,7 +100,8 @@ size_t sw_smem_bytes(uint32_t n_objects, uint32_t n_nodes, uint32_t n_lights, bo
 template <int MODE, bool PROF>
 __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(SceneView s, const __grid_constant__ Frame f, SwOut out,
                                                                            const __grid_constant__ BruteParam bp,
-                                                                           const __grid_constant__ FastParam fp, uint32_t n_fast_pairs, uint32_t n_fast_spheres) {
+                                                                           const __grid_constant__ FastParam fp, uint32_t n_fast_pairs, uint32_t n_fast_spheres,
+                                                                           const __grid_constant__ CullParam cull) {
     constexpr bool BRUTE = MODE != 0;
     constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NGRP = SPT * NW;
     extern __shared__ float4 smem[];
@@ -134,14 +135,17 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     // A CTA holds TWO ranges, the one it is consuming and the next, so that an iteration never runs short of work items
     // before the frame does (a slot that finds no work item leaves the window for good).
     __shared__ unsigned long long s_rng[2][4];       // [parity][lo, hi, lo2, hi2): current and next range of the work list
-    auto grab = [&](unsigned long long* dst) {       // one thread
+    __shared__ uint32_t s_org[2][4];                 // [parity][sample, pixel of lo; sample, pixel of lo2]: work item w = sample * npix + pixel
+    auto grab = [&](unsigned long long* dst, uint32_t* org) {       // one thread
         const unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(out.work_next);
         const unsigned long long left = f.total_work > cur ? f.total_work - cur : 0ull;
         unsigned long long size = left / (4ull * gridDim.x);       // measured at 128 spp: /2 5.7, /4 6.40, one window 6.39, static 6.27 Gsamples/s
         if (size < (unsigned long long)kSwSlots) size = kSwSlots;
+        if (size > (1ull << 30)) size = 1ull << 30;                // offsets inside a range stay 32-bit
         const unsigned long long c = atomicAdd(out.work_next, size);
         dst[0] = c < f.total_work ? c : f.total_work;
         dst[1] = c + size < f.total_work ? c + size : f.total_work;
+        org[0] = (uint32_t)(dst[0] / f.npix); org[1] = (uint32_t)(dst[0] % f.npix);   // the only 64-bit divisions: once per range
     };
 
     // ---- stage the scene once
@@ -158,8 +162,10 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     // the planar-entry scan (pt_wave.cuh: fast_pair)
     // A camera ray that misses the padded scene bounds misses every primitive (the slab test is conservative, the one the LBVH
     // walk relies on): at 1920x1080 ~40 % of the default scene's primary rays end here, warp-uniformly (re-seeding is dense).
-    auto trace_closest = [&](float3 ro, float3 rd, bool primary, float& t, int& id) {
-        if (BRUTE && primary) {
+    // MODE >= 2: the per-entry pixel rectangles of `cull` do the same per pair of triangles (closest_hit_param_culled).
+    auto trace_closest = [&](float3 ro, float3 rd, bool primary, uint32_t px, uint32_t py, float& t, int& id) {
+        if (MODE >= 2 && primary) { closest_hit_param_culled<MODE == 2>(bp, cull, g, px, py, ro, rd, f.t_min, t, id); return; }
+        if (MODE == 1 && primary) {
             const float3 inv = v3(__frcp_rn(rd.x), __frcp_rn(rd.y), __frcp_rn(rd.z));
             float tn;
             if (!slab(f.blo, f.bhi, ro, inv, f.t_min, FLT_MAX, tn)) { t = FLT_MAX; id = -1; return; }
@@ -181,7 +187,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         s_len[0] = (uint32_t)kSwSlots << 16; s_tile = 0;
         for (int c = 0; c < 4; ++c) s_cls[0][c] = s_cls[1][c] = 0;
         if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = 0; }
-        grab(s_rng[0]); grab(s_rng[0] + 2);
+        grab(s_rng[0], s_org[0]); grab(s_rng[0] + 2, s_org[0] + 2);
     }
     uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // per-lane counters, reduced once at the end
     uint64_t n_primary = 0;                                          // work items this CTA started (uniform)
@@ -193,16 +199,28 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         // the end of the range, are dead: they join no class list and phase A never touches them.
         const uint32_t par = iters & 1;
         const uint32_t n_cont = s_len[par] & 0xffffu, n_regen = s_len[par] >> 16;
-        const uint64_t base = s_rng[par][0], avail1 = s_rng[par][1] - base, base2 = s_rng[par][2], avail = avail1 + (s_rng[par][3] - base2);
+        const uint64_t base = s_rng[par][0], base2 = s_rng[par][2];
+        const uint32_t avail1 = (uint32_t)(s_rng[par][1] - base), avail2 = (uint32_t)(s_rng[par][3] - base2);   // each range is at most 2^30 items
+        const uint64_t avail = (uint64_t)avail1 + avail2;
         const uint32_t n_new = avail < n_regen ? (uint32_t)avail : n_regen;
+        const uint32_t smp1 = s_org[par][0], pix1 = s_org[par][1], smp2 = s_org[par][2], pix2 = s_org[par][3];
         if (n_cont + n_new == 0) break;                              // uniform: both ranges are empty only when the frame's work list is
         if (tid == 0) {
             s_len[par ^ 1] = 0; s_tile = 0;
             unsigned long long* nx = s_rng[par ^ 1];
+            uint32_t* no = s_org[par ^ 1];
+            auto advance = [&](uint32_t smp, uint32_t pix, uint32_t by, uint32_t* o) {   // by <= kSwSlots
+                const uint32_t p = pix + by, q = p / f.npix;
+                o[0] = smp + q; o[1] = p - q * f.npix;
+            };
             if (n_new >= avail1) {                                   // current range used up: the next one becomes current, a new next is fetched
                 nx[0] = base2 + (n_new - avail1); nx[1] = s_rng[par][3];
-                grab(nx + 2);                                        // (empty once the frame is handed out)
-            } else { nx[0] = base + n_new; nx[1] = s_rng[par][1]; nx[2] = base2; nx[3] = s_rng[par][3]; }
+                advance(smp2, pix2, n_new - avail1, no);
+                grab(nx + 2, no + 2);                                // (empty once the frame is handed out)
+            } else {
+                nx[0] = base + n_new; nx[1] = s_rng[par][1]; nx[2] = base2; nx[3] = s_rng[par][3];
+                advance(smp1, pix1, n_new, no); no[2] = smp2; no[3] = pix2;
+            }
         }
 #pragma unroll 1                                                     // one copy of the scan: the instruction cache is 32 KB
         for (int k = 0; k < SPT; ++k) {
@@ -213,16 +231,18 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                 j = s_list[e];
                 PT_CHECK(j < (uint32_t)kSwSlots);
                 float4 ro, rd;
+                uint32_t px = 0, py = 0;                              // pixel column and flipped row of a camera ray
                 if (seed) {
                     uint2 m;
-                    const uint64_t k_new = kSwSlots - 1 - e;
-                    make_primary(f, k_new < avail1 ? base + k_new : base2 + (k_new - avail1), ro, rd, m);
+                    const uint32_t k_new = kSwSlots - 1 - e;
+                    const bool first = k_new < avail1;
+                    make_primary_at(f, first ? smp1 : smp2, first ? pix1 + k_new : pix2 + (k_new - avail1), ro, rd, m, px, py);
                     s_ro[j] = ro; s_rd[j] = rd; s_meta[j] = m; s_beta[j] = make_float4(1.f, 1.f, 1.f, 0.f);
                 } else {
                     ro = s_ro[j]; rd = s_rd[j];
                 }
                 float t; int id;
-                trace_closest(v3(ro), v3(rd), seed, t, id);
+                trace_closest(v3(ro), v3(rd), seed, px, py, t, id);
                 PT_CHECK(id < (int)s.n_objects);
                 s_hit[j] = make_uint2(__float_as_uint(t), (uint32_t)id);
                 if (id < 0) c = CLS_MISS;
@@ -347,6 +367,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
     const int mode = !brute ? 0 : pick_scan_mode(scene, rl.cam, rl.prm.traversal);
     const BruteParam bp = make_brute_param(scene);
     const FastParam fp = make_fast_param(scene);
+    const CullParam cull = make_cull_param(scene, rl.cam, mode >= 2);
     const uint32_t n_fast_pairs = scene.n_fast_pairs;
     int occ = 0, rc;
     auto with_kernel = [&](auto&& fn) -> int {
@@ -394,7 +415,7 @@ int smem_wavefront_render(pt_context* ctx, const RenderLaunch& rl, bool brute, p
         while (ctx->prof_events.size() < 2) { cudaEvent_t e; PT_CUDA_CHECK(ctx, cudaEventCreate(&e)); ctx->prof_events.push_back(e); }
         PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[0], st));
     }
-    with_kernel([&](auto kernel) { kernel<<<grid, kSwBlock, smem, st>>>(sv, f, out, bp, fp, n_fast_pairs, scene.n_fast_spheres); return PT_OK; });
+    with_kernel([&](auto kernel) { kernel<<<grid, kSwBlock, smem, st>>>(sv, f, out, bp, fp, n_fast_pairs, scene.n_fast_spheres, cull); return PT_OK; });
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     if (profile) PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->prof_events[1], st));
     if (stats) {
@@ -531,7 +552,8 @@ int smem_wavefront_render_noalloc(pt_context* ctx, const SceneDev& scene, const 
     PT_CUDA_CHECK(ctx, cudaMemsetAsync(out.work_next, 0, 8, st));
     const FastParam fp = make_fast_param(scene);
     const BruteParam bp = make_brute_param(scene);
-    with_kernel([&](auto kernel) { kernel<<<(uint32_t)grid, kSwBlock, smem, st>>>(sv, f, out, bp, fp, scene.n_fast_pairs, scene.n_fast_spheres); return PT_OK; });
+    const CullParam cull = make_cull_param(scene, cam, mode >= 2);
+    with_kernel([&](auto kernel) { kernel<<<(uint32_t)grid, kSwBlock, smem, st>>>(sv, f, out, bp, fp, scene.n_fast_pairs, scene.n_fast_spheres, cull); return PT_OK; });
     PT_CUDA_CHECK(ctx, cudaGetLastError());
     return resolve_launch(ctx, d_accum, cam.width, cam.height, prm.spp, d_radiance, d_rgba);
 }

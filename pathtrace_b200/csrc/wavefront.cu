@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary(SceneView s, const __g
 template <bool CHECKED>
 __global__ void __launch_bounds__(kBlock) k_trace_primary_param(SceneView s, const __grid_constant__ Frame f, int jitter, float ox, float oy, uint32_t sample,
                                                                 int32_t* __restrict__ obj, float* __restrict__ tt, float* __restrict__ dirs,
-                                                                const __grid_constant__ BruteParam bp) {
+                                                                const __grid_constant__ BruteParam bp, const __grid_constant__ CullParam cull) {
     extern __shared__ float4 smem[];
     Geo<true> g = stage_scene<true>(s, smem, false);
     uint32_t i = blockIdx.x * kBlock + threadIdx.x;
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(kBlock) k_trace_primary_param(SceneView s, con
     }
     float3 d = camera_dir(f.cam, x, f.cam.height - 1 - y, ox, oy);
     float t; int id;
-    closest_hit_param<CHECKED>(bp, g, f.cam.origin, d, f.t_min, t, id);
+    closest_hit_param_culled<CHECKED>(bp, cull, g, x, f.cam.height - 1 - y, f.cam.origin, d, f.t_min, t, id);   // what the wavefront's camera rays run
     obj[i] = id;
     tt[i] = id >= 0 ? t : __int_as_float(0x7f800000);
     if (dirs) { dirs[3 * (size_t)i] = d.x; dirs[3 * (size_t)i + 1] = d.y; dirs[3 * (size_t)i + 2] = d.z; }
@@ -601,12 +601,14 @@ int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_cam
     }
     if (scan >= 2) {   // the constant-bank scan the shared-memory wavefront runs on this scene
         const BruteParam bp = make_brute_param(scene);
+        // the pixel-rectangle cull holds for ray offsets inside the pixel cell (the jitter is in (0, 1))
+        const CullParam cull = make_cull_param(scene, cam, jitter || (ox >= 0.0f && ox <= 1.0f && oy >= 0.0f && oy <= 1.0f));
         if (scan == 2) {   // (scan 3 and 4 trace primary rays with the same in-domain pair test)
             int rc = set_smem(ctx, k_trace_primary_param<true>, mode.smem_bytes); if (rc) return rc;
-            k_trace_primary_param<true><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp);
+            k_trace_primary_param<true><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp, cull);
         } else {
             int rc = set_smem(ctx, k_trace_primary_param<false>, mode.smem_bytes); if (rc) return rc;
-            k_trace_primary_param<false><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp);
+            k_trace_primary_param<false><<<grid, kBlock, mode.smem_bytes, ctx->stream>>>(sv, f, jitter, ox, oy, sample, d_obj, d_t, d_dir, bp, cull);
         }
         PT_CUDA_CHECK(ctx, cudaGetLastError());
         if (launches) *launches += 1;

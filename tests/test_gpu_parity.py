@@ -236,3 +236,50 @@ def test_forced_bvh_on_trivial_scenes(n, hbm_queues, oracle, gpu_ctx):
     assert np.isfinite(rad).all() and st["rays_primary"] == 4 * 48 * 32
     if n == 0:
         assert not rad.any()
+
+
+def _odd_cameras():
+    from pathtrace_b200.objects import Camera, Vector3 as V
+    W, H = 192, 108
+    return {
+        "default": Camera.new(V.new(0, 0, 2), W, H, 1.0, 35.0),
+        "inside_room": Camera.new(V.new(0.1, -0.2, -1.6), W, H, 1.0, 80.0),                       # walls extend behind the camera plane
+        "oblique": Camera.look_at(V.new(2.5, 1.5, 1.0), V.new(0, -0.3, -2), V.new(0, 1, 0), W, H, 40.0),
+        "rolled": Camera.look_at(V.new(-1.5, 0.2, 1.5), V.new(0.4, -0.6, -2), V.new(0.3, 1, 0.1), W, H, 25.0),
+        "edge_on_floor": Camera.new(V.new(0, -1.0 + 1e-4, 2), W, H, 1.0, 35.0),                   # the floor's plane passes (almost) through the eye
+        "in_left_wall_plane": Camera.new(V.new(-1.0, 0, 2), W, H, 1.0, 50.0),                     # exactly in a wall's plane
+        "from_behind": Camera.look_at(V.new(0, 0, -6), V.new(0, 0, -2), V.new(0, 1, 0), W, H, 35.0),
+        "looking_away": Camera.look_at(V.new(0, 0, 2), V.new(0, 0, 6), V.new(0, 1, 0), W, H, 35.0),   # everything behind
+        "inside_sphere": Camera.look_at(V.new(0.4, -0.6, -2.0), V.new(0, 0.5, -3), V.new(0, 1, 0), W, H, 70.0),
+        "telephoto_on_light": Camera.look_at(V.new(0, -0.9, 0.5), V.new(0, 0.99, -2), V.new(0, 1, 0), W, H, 6.0),
+    }
+
+
+@pytest.mark.parametrize("cam_name", list(_odd_cameras()))
+@pytest.mark.parametrize("scene_name", ["default", "zoo"])
+def test_primary_cull_is_exact_for_any_camera(cam_name, scene_name, oracle, gpu_ctx):
+    """The constant-bank scan of camera rays skips entries whose projected pixel rectangle no lane of the warp touches
+    (pt_wave.cuh: closest_hit_param_culled).  For every camera pose — including those where the host cannot bound an entry and
+    must fall back to the full screen — ids and t equal the scan table's (no cull) and the FP32 oracle's bit for bit."""
+    from pathtrace_b200 import api, scenes
+    sh, mt, _ = scenes.default_scene(8, 8) if scene_name == "default" else scenes.material_zoo_scene(8, 8)
+    cam = _odd_cameras()[cam_name]
+    sc = api.Scene(gpu_ctx, sh, mt)
+    runs = [dict(jitter=True, sample=s) for s in (0, 1, 7)] + [dict(jitter=False, ox=ox, oy=oy) for ox, oy in ((0.0, 0.0), (1.0, 1.0), (0.5, 0.5), (0.0, 1.0))]
+    n_hit = 0
+    for kw in runs:
+        ids, t, _ = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal="brute_exact"), **kw)
+        for other in ("brute_table", "brute_param_checked"):
+            ids2, t2, _ = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal=other), **kw)
+            assert np.array_equal(ids, ids2), (kw, other, int((ids != ids2).sum()))
+            assert np.array_equal(t.view(np.uint32), t2.view(np.uint32)), (kw, other)
+        n_hit += int((ids >= 0).sum())
+    rid, rt, _ = oracle.trace_primary(oracle_camera(oracle, cam), sh, mt, precision="f32", jitter=True, sample=7)
+    ids, t, _ = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal="brute_exact"), jitter=True, sample=7)
+    sc.close()
+    assert np.array_equal(ids, rid)
+    assert np.array_equal(t[rid >= 0].view(np.uint32), rt[rid >= 0].astype(np.float32).view(np.uint32))
+    if cam_name != "looking_away":
+        assert n_hit > 0
+    else:
+        assert n_hit == 0
