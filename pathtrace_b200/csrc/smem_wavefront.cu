@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     __shared__ uint32_t s_cls[2][4];           // entries per class list
     __shared__ uint32_t s_len[2];              // next work list: continuing entries (front) | entries to re-seed (back) << 16
     __shared__ uint32_t s_tile;
+    __shared__ unsigned long long s_tot[3];    // statistics of this CTA: vertices, scattered rays, shadow rays
     __shared__ unsigned long long s_clk[3];    // PROF: t_prev, T+S, A
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
@@ -186,10 +187,21 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     if (tid == 0) {
         s_len[0] = (uint32_t)kSwSlots << 16; s_tile = 0;
         for (int c = 0; c < 4; ++c) s_cls[0][c] = s_cls[1][c] = 0;
+        s_tot[0] = s_tot[1] = s_tot[2] = 0ull;
         if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = 0; }
         grab(s_rng[0], s_org[0]); grab(s_rng[0] + 2, s_org[0] + 2);
     }
-    uint32_t c_vertex = 0, c_scatter = 0, c_shadow = 0, iters = 0;   // per-lane counters, reduced once at the end
+    // Statistics: ONE packed per-lane register (vertices | scattered rays << 10 | shadow rays << 20; a lane adds at most kSwSpt of
+    // each per iteration), flushed into 64-bit shared totals every 64 iterations.  Three separate counters were spilled to local
+    // memory by ptxas at the 80-register cap and every tile waited on their reloads.
+    static_assert(64 * kSwSpt < 1024, "the packed per-lane statistics hold 10 bits per field between flushes");
+    uint32_t c_pack = 0, iters = 0;
+    auto flush_stats = [&]() {
+        const uint32_t v = __reduce_add_sync(0xffffffffu, c_pack & 1023u), sc2 = __reduce_add_sync(0xffffffffu, (c_pack >> 10) & 1023u),
+                       sh = __reduce_add_sync(0xffffffffu, c_pack >> 20);
+        if (lane == 0) { atomicAdd(&s_tot[0], (unsigned long long)v); atomicAdd(&s_tot[1], (unsigned long long)sc2); atomicAdd(&s_tot[2], (unsigned long long)sh); }
+        c_pack = 0;
+    };
     uint64_t n_primary = 0;                                          // work items this CTA started (uniform)
     __syncthreads();
 
@@ -289,7 +301,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             if (alive) {
                 VertexOut vo = shade_vertex(sc, f, mis, s_ro[j], s_rd[j], v3(s_beta[j]), s_hit[j], meta);
                 finished = vo.finished;
-                c_vertex += vo.vertex ? 1u : 0u;
+                c_pack += (vo.vertex ? 1u : 0u) + (vo.finished ? 0u : 1u << 10) + (vo.emit_shadow ? 1u << 20 : 0u);
                 p_hit = v3(vo.new_ro);                                // a finished path may still owe its last vertex's shadow ray
                 emit_shadow = vo.emit_shadow; sh_d = vo.sh_d; sh_c = vo.sh_c; sh_tmax = vo.sh_tmax;
                 if (vo.finished) {
@@ -298,13 +310,11 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                 } else {
                     s_ro[j] = vo.new_ro; s_rd[j] = vo.new_rd; s_meta[j] = vo.new_meta;
                     s_beta[j] = make_float4(vo.new_beta.x, vo.new_beta.y, vo.new_beta.z, 0.f);
-                    ++c_scatter;
                 }
             }
             // K5 in line: the shadow ray starts at the hit point (the new ray origin) and is traced by the lane that shaded
             // the vertex; unoccluded contributions go straight to the pixel (rendering.rs:62-80).
             if (emit_shadow) {
-                ++c_shadow;
                 if (!trace_any(p_hit, sh_d, sh_tmax)) atomicAdd(f.accum + META_PIXEL(meta), make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f));
             }
             // next work list: continuing slots from the front, slots to re-seed from the back
@@ -319,19 +329,16 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         }
         ++iters;
         n_primary += n_new;
+        if ((iters & 63u) == 0u) flush_stats();
         __syncthreads();
         if (PROF && tid == 0) { unsigned long long t = clock64(); s_clk[2] += t - s_clk[0]; s_clk[0] = t; }
     }
 
     // ---- bookkeeping
-    __shared__ uint32_t s_stats[3];
-    if (tid < 3) s_stats[tid] = 0;
-    __syncthreads();
-    c_shadow = __reduce_add_sync(0xffffffffu, c_shadow); c_scatter = __reduce_add_sync(0xffffffffu, c_scatter); c_vertex = __reduce_add_sync(0xffffffffu, c_vertex);
-    if (lane == 0) { atomicAdd(&s_stats[0], c_shadow); atomicAdd(&s_stats[1], c_scatter); atomicAdd(&s_stats[2], c_vertex); }
+    flush_stats();
     __syncthreads();
     if (tid == 0) {
-        out.block_stats[blockIdx.x] = make_uint4((uint32_t)n_primary, s_stats[0], s_stats[1], s_stats[2]);
+        out.block_stats[blockIdx.x] = make_uint4((uint32_t)n_primary, (uint32_t)s_tot[2], (uint32_t)s_tot[1], (uint32_t)s_tot[0]);
         out.block_iters[blockIdx.x] = iters;
         if (PROF) { out.block_clk[3 * blockIdx.x] = s_clk[1]; out.block_clk[3 * blockIdx.x + 1] = s_clk[2]; out.block_clk[3 * blockIdx.x + 2] = 0; }
     }
