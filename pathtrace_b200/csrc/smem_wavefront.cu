@@ -63,14 +63,15 @@ PT_DEV uint32_t atom_add_shared(uint32_t* p, uint32_t v) {
     return old;
 }
 
-// The same add issued by ONE elected lane of a converged warp, result broadcast to all lanes.  Written with elect.sync
-// because ptxas wraps every shared-memory atomic it cannot prove single-lane in a vote / find-leader / popc / shuffle
-// sequence (17 instructions around `if (lane == 0) atom`); after ELECT it emits the bare ATOMS.
-PT_DEV uint32_t warp_atom_add_shared(uint32_t* p, uint32_t v) {
-    uint32_t old = 0, leader;
+// A 64-bit add issued by ONE elected lane of a converged warp, result broadcast to all lanes.  Written with elect.sync because
+// ptxas wraps every shared-memory atomic it cannot prove single-lane in a vote / find-leader / popc / shuffle sequence (17
+// instructions around `if (lane == 0) atom`); after ELECT it emits the bare ATOMS.
+PT_DEV unsigned long long warp_atom_add_shared64(unsigned long long* p, unsigned long long v) {
+    unsigned long long old = 0;
+    uint32_t leader;
     asm volatile(
-        "{\n .reg .pred q;\n elect.sync %1|q, 0xffffffff;\n @q atom.shared.add.u32 %0, [%2], %3;\n}"
-        : "+r"(old), "=r"(leader) : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+        "{\n .reg .pred q;\n elect.sync %1|q, 0xffffffff;\n @q atom.shared.add.u64 %0, [%2], %3;\n}"
+        : "+l"(old), "=r"(leader) : "r"((uint32_t)__cvta_generic_to_shared(p)), "l"(v) : "memory");
     return __shfl_sync(0xffffffffu, old, leader);
 }
 
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
                                                                            const __grid_constant__ FastParam fp, uint32_t n_fast_pairs, uint32_t n_fast_spheres,
                                                                            const __grid_constant__ CullParam cull) {
     constexpr bool BRUTE = MODE != 0;
-    constexpr int NW = kSwBlock / 32, SPT = kSwSpt, NGRP = SPT * NW;
+    constexpr int SPT = kSwSpt;
     extern __shared__ float4 smem[];
     float4* s_ro = smem;
     float4* s_rd = s_ro + kSwSlots;
@@ -124,12 +125,13 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     // Counters alternate between two copies so that none is reset while a straggler may still read it: iteration i counts the
     // classes in s_cls[i & 1] and reads its work list sizes from s_len[i & 1]; phase A of iteration i fills s_len[(i + 1) & 1].
     __shared__ uint32_t s_cls[2][4];           // entries per class list
-    __shared__ uint32_t s_len[2];              // next work list: continuing entries (front) | entries to re-seed (back) << 16
-    __shared__ uint32_t s_tile;
+    // next work list: continuing entries (front) | entries to re-seed (back) << 16, and in the upper half the tile counter of the
+    // phase A that fills it — one 64-bit atomic per tile appends the finished tile's slots AND fetches the next tile
+    __shared__ unsigned long long s_len[2];
     __shared__ unsigned long long s_tot[3];    // statistics of this CTA: vertices, scattered rays, shadow rays
     __shared__ unsigned long long s_clk[3];    // PROF: t_prev, T+S, A
 
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, lt_mask = (1u << lane) - 1u;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, lt_mask = (1u << lane) - 1u;
     const bool mis = f.strategy == PT_STRATEGY_MIS;
     // Work is handed to the CTAs in chunks from one global counter (guided self-scheduling: a quarter of an even share of what
     // is left, never less than one window), so no CTA is left finishing a static range while the others idle.
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
     // ---- the first work list re-seeds every slot
     for (uint32_t i = tid; i < (uint32_t)kSwSlots; i += kSwBlock) s_list[i] = (uint16_t)i;
     if (tid == 0) {
-        s_len[0] = (uint32_t)kSwSlots << 16; s_tile = 0;
+        s_len[0] = (unsigned long long)kSwSlots << 16; s_len[1] = 0ull;
         for (int c = 0; c < 4; ++c) s_cls[0][c] = s_cls[1][c] = 0;
         s_tot[0] = s_tot[1] = s_tot[2] = 0ull;
         if (PROF) { s_clk[0] = clock64(); s_clk[1] = s_clk[2] = 0; }
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         // from the back (entry kSwSlots-1 first) while the CTA's range lasts.  Entries in between, and re-seed entries past
         // the end of the range, are dead: they join no class list and phase A never touches them.
         const uint32_t par = iters & 1;
-        const uint32_t n_cont = s_len[par] & 0xffffu, n_regen = s_len[par] >> 16;
+        const uint32_t n_cont = (uint32_t)s_len[par] & 0xffffu, n_regen = ((uint32_t)s_len[par] >> 16) & 0xffffu;
         const uint64_t base = s_rng[par][0], base2 = s_rng[par][2];
         const uint32_t avail1 = (uint32_t)(s_rng[par][1] - base), avail2 = (uint32_t)(s_rng[par][3] - base2);   // each range is at most 2^30 items
         const uint64_t avail = (uint64_t)avail1 + avail2;
@@ -218,7 +220,7 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         const uint32_t smp1 = s_org[par][0], pix1 = s_org[par][1], smp2 = s_org[par][2], pix2 = s_org[par][3];
         if (n_cont + n_new == 0) break;                              // uniform: both ranges are empty only when the frame's work list is
         if (tid == 0) {
-            s_len[par ^ 1] = 0; s_tile = 0;
+            s_len[par ^ 1] = 0ull;
             unsigned long long* nx = s_rng[par ^ 1];
             uint32_t* no = s_org[par ^ 1];
             auto advance = [&](uint32_t smp, uint32_t pix, uint32_t by, uint32_t* o) {   // by <= kSwSlots
@@ -283,8 +285,9 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
         const uint32_t i0 = (n_mir + 31) / 32, i1 = i0 + (n_dif + 31) / 32, i2 = i1 + (n_emi + 31) / 32, i3 = i2 + (n_mis + 31) / 32;
 
         // ---- phase A: dynamic tiles of the class-sorted list
+        unsigned long long got = warp_atom_add_shared64(&s_len[par ^ 1], 1ull << 32);
         while (true) {
-            const uint32_t tile = warp_atom_add_shared(&s_tile, 1u);
+            const uint32_t tile = (uint32_t)(got >> 32);
             if (tile >= i3) break;
             uint32_t idx, cnt; const uint16_t* ord; bool fwd;         // expensive tiles first: mirror, diffuse, emissive, miss
             if (tile < i0)      { idx = tile * 32 + lane;        cnt = n_mir; ord = s_ord_a; fwd = true; }
@@ -321,8 +324,8 @@ __global__ void __launch_bounds__(kSwBlock, kSwMinBlocks) k_smem_wavefront(Scene
             {
                 const uint32_t fin = __ballot_sync(0xffffffffu, alive && finished), con = __ballot_sync(0xffffffffu, alive && !finished);
                 // one atomic for both ends of the list: continuing count in the low half, re-seed count in the high half
-                const uint32_t b = warp_atom_add_shared(&s_len[par ^ 1], (uint32_t)__popc(con) | ((uint32_t)__popc(fin) << 16));
-                const uint32_t bfin = b >> 16, bcon = b & 0xffffu;
+                got = warp_atom_add_shared64(&s_len[par ^ 1], (unsigned long long)((uint32_t)__popc(con) | ((uint32_t)__popc(fin) << 16)) | (1ull << 32));
+                const uint32_t b = (uint32_t)got, bfin = b >> 16, bcon = b & 0xffffu;
                 PT_CHECK(bfin + bcon + __popc(fin) + __popc(con) <= (uint32_t)kSwSlots);
                 if (alive) s_list[finished ? kSwSlots - 1 - (bfin + __popc(fin & lt_mask)) : bcon + __popc(con & lt_mask)] = (uint16_t)j;
             }
