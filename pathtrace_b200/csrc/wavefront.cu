@@ -127,8 +127,14 @@ __global__ void __launch_bounds__(kBlock) k_trace_shadow(Pool pool, SceneView s,
 #ifndef PT_STREAM_MINB
 #define PT_STREAM_MINB 5   // resident CTAs per SM asked of the L1/L2 walk
 #endif
+// The walk with the scene in shared memory runs larger CTAs than the rest: more warps share each staged copy of the scene
+// (C3: 79 KB, two copies fit), so the warp count is set by the register file (32 warps at 64 registers) and not by the copies.
+#ifndef PT_STREAM_BLOCK_SMEM
+#define PT_STREAM_BLOCK_SMEM 512    // C3 at 16 spp: 256 threads (2 CTAs per SM) 1395, 512 (2 CTAs) 1443, 768 (1 CTA) 1371, 1024 (1 CTA) 1433 Msamples/s
+#endif
+constexpr int kStreamBlockSmem = PT_STREAM_BLOCK_SMEM;
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t chunk, unsigned long long* __restrict__ next_chunk,
+__global__ void __launch_bounds__(SMEM ? kStreamBlockSmem : kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_closest_stream(Pool pool, SceneView s, float t_min, uint32_t chunk, unsigned long long* __restrict__ next_chunk,
                                                                                             unsigned long long* __restrict__ walk_counters) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
@@ -158,7 +164,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_clo
     bvh_stream<SMEM, false, COUNT>(g, t_min, next, finish, walk_counters);
 }
 template <bool SMEM, bool COUNT>
-__global__ void __launch_bounds__(kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t chunk,
+__global__ void __launch_bounds__(SMEM ? kStreamBlockSmem : kBlock, SMEM ? 1 : PT_STREAM_MINB) k_trace_shadow_stream(Pool pool, SceneView s, float t_min, float4* __restrict__ accum, uint32_t chunk,
                                                                                            unsigned long long* __restrict__ next_chunk, unsigned long long* __restrict__ walk_counters) {
     extern __shared__ float4 smem[];
     Geo<SMEM> g = stage_scene<SMEM>(s, smem, true);
@@ -682,13 +688,14 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     const bool stream_bvh = !mode.brute;
     const bool count = stream_bvh && (rl.prm.flags & PT_FLAG_COUNTERS) != 0;
     uint32_t stream_grid = 0, stream_chunk = 0;
+    const int stream_block = mode.smem ? kStreamBlockSmem : kBlock;
     if (stream_bvh) {
         int occ_c = 0, occ_s = 0;
         auto setup = [&](auto kc, auto ks, size_t bytes) -> int {
             int rc2 = set_smem(ctx, kc, bytes); if (rc2) return rc2;
             rc2 = set_smem(ctx, ks, bytes); if (rc2) return rc2;
-            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, kc, kBlock, bytes));
-            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, ks, kBlock, bytes));
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, kc, stream_block, bytes));
+            PT_CUDA_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_s, ks, stream_block, bytes));
             return PT_OK;
         };
         if (mode.smem) rc = count ? setup(k_trace_closest_stream<true, true>, k_trace_shadow_stream<true, true>, mode.smem_bytes)
@@ -736,8 +743,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
 #define TRACE(S, B) k_trace_closest<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min)
             prof_begin(PT_K_TRACE_CLOSEST);
             if (stream_bvh) {
-                if (mode.smem && count) k_trace_closest_stream<true, true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
-                else if (mode.smem) k_trace_closest_stream<true, false><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
+                if (mode.smem && count) k_trace_closest_stream<true, true><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
+                else if (mode.smem) k_trace_closest_stream<true, false><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
                 else if (count) k_trace_closest_stream<false, true><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
                 else k_trace_closest_stream<false, false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, stream_chunk, cur_c, walk);
             } else PT_DISPATCH(mode, TRACE);
@@ -751,8 +758,8 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
                 prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
                 if (stream_bvh) {
-                    if (mode.smem && count) k_trace_shadow_stream<true, true><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
-                    else if (mode.smem) k_trace_shadow_stream<true, false><<<stream_grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    if (mode.smem && count) k_trace_shadow_stream<true, true><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else if (mode.smem) k_trace_shadow_stream<true, false><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
                     else if (count) k_trace_shadow_stream<false, true><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
                     else k_trace_shadow_stream<false, false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
                 } else PT_DISPATCH(mode, SHADOW);
