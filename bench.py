@@ -169,6 +169,16 @@ def other_configs(args, rank, world, ctx, ext, dev):
     keys = ("samples", "rays_primary", "rays_shadow", "rays_scattered", "path_vertices", "kernel_launches", "nodes_visited", "prim_tests")
     out = {}
 
+    # ---- C1: the reference's own default workload, world.rs:16-18: 400x400 at 3000 spp (full size: 4.8e8 samples)
+    sh, mt, cam = scenes.default_scene(400, 400)
+    sc = api.Scene(ctx, sh, mt)
+    ms, st = _frame(api, dist, torch, ctx, sc, cam, 3000, rank, world, ext, dev, reps=1)
+    tot = _sum_over_ranks(torch, dist, dev, world, st, keys)
+    out["C1"] = {"workload": "default Cornell scene 400x400 3000spp MIS (WIDTH/HEIGHT/SAMPLE_NUM of world.rs:16-18, full size)", "n_gpus": world,
+                 "value": 400 * 400 * 3000 / ms / 1e3, "unit": "Msamples/s", "ms": ms, "kernel_launches": int(tot["kernel_launches"]),
+                 "mrays_per_s": (tot["rays_primary"] + tot["rays_shadow"] + tot["rays_scattered"]) / ms / 1e3}
+    sc.close()
+
     # ---- C3: 495-object random spheres, 3840x2160 (formulation B, LBVH in shared memory)
     sh, mt, cam = scenes.random_spheres_scene(3840, 2160)
     sc = api.Scene(ctx, sh, mt)
