@@ -186,6 +186,9 @@ void pt_context_destroy(pt_context* ctx) {
     if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : ctx->prof_events) cudaEventDestroy(ev);
+    if (ctx->ev_shaded) cudaEventDestroy(ctx->ev_shaded);
+    if (ctx->ev_shadowed) cudaEventDestroy(ctx->ev_shadowed);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -57,6 +57,9 @@ struct pt_context {
     uint64_t* d_counters = nullptr;   // device counters block
     uint64_t* h_counters = nullptr;   // pinned mirror
     std::vector<cudaEvent_t> prof_events;   // PT_FLAG_PROFILE: start/stop pairs per launch
+    // HBM-queue wavefront: the shadow rays of bounce i are traced on a second stream while bounce i + 1 finds its closest hits
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_shaded = nullptr, ev_shadowed = nullptr;
 };
 
 struct pt_scene {

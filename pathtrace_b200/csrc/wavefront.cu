@@ -731,6 +731,20 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
     k_generate<<<grid, kBlock, 0, st>>>(pool, f); launches++;
     prof_end();
     const bool mis = rl.prm.strategy == PT_STRATEGY_MIS && scene.n_lights > 0;
+    // The shadow rays of a bounce and the closest hits of the next one are independent once the bounce is shaded: the shadow
+    // launch goes to a second stream and the two resident grids fill each other's tails (each launch ends with a few long
+    // walks on an otherwise idle GPU).  Off under PT_FLAG_PROFILE, whose per-class event times assume serial launches.
+    const bool overlap = mis && stream_bvh && !profile;
+    cudaStream_t st_sh = st;
+    if (overlap) {
+        if (!ctx->stream2) {
+            PT_CUDA_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+            PT_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_shaded, cudaEventDisableTiming));
+            PT_CUDA_CHECK(ctx, cudaEventCreateWithFlags(&ctx->ev_shadowed, cudaEventDisableTiming));
+        }
+        st_sh = ctx->stream2;
+    }
+    bool shadow_pending = false;
     bool done = false;
     uint64_t nodes_visited = 0, prim_tests = 0;
     unsigned long long* walk = reinterpret_cast<unsigned long long*>(ctx->d_counters + C_WALK);
@@ -751,24 +765,31 @@ int wavefront_render(pt_context* ctx, const RenderLaunch& rl, pt_stats* stats) {
             prof_end();
 #undef TRACE
             prof_begin(PT_K_SHADE);
+            if (overlap && shadow_pending) PT_CUDA_CHECK(ctx, cudaStreamWaitEvent(st, ctx->ev_shadowed, 0));   // shading rewrites the shadow queue
             k_shade<<<sgrid, kShadeBlock, 0, st>>>(pool, sv, f, ctx->d_counters, it);
             prof_end();
             launches += 2;
             if (mis) {
+                if (overlap) {
+                    PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_shaded, st));
+                    PT_CUDA_CHECK(ctx, cudaStreamWaitEvent(st_sh, ctx->ev_shaded, 0));
+                }
                 prof_begin(PT_K_TRACE_SHADOW);
 #define SHADOW(S, B) k_trace_shadow<S, B><<<grid, kBlock, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum)
                 if (stream_bvh) {
-                    if (mode.smem && count) k_trace_shadow_stream<true, true><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
-                    else if (mode.smem) k_trace_shadow_stream<true, false><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
-                    else if (count) k_trace_shadow_stream<false, true><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
-                    else k_trace_shadow_stream<false, false><<<stream_grid, kBlock, 0, st>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    if (mode.smem && count) k_trace_shadow_stream<true, true><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st_sh>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else if (mode.smem) k_trace_shadow_stream<true, false><<<stream_grid, kStreamBlockSmem, mode.smem_bytes, st_sh>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else if (count) k_trace_shadow_stream<false, true><<<stream_grid, kBlock, 0, st_sh>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
+                    else k_trace_shadow_stream<false, false><<<stream_grid, kBlock, 0, st_sh>>>(pool, sv, f.t_min, f.accum, stream_chunk, cur_s, walk);
                 } else PT_DISPATCH(mode, SHADOW);
 #undef SHADOW
                 prof_end();
                 launches++;
+                if (overlap) { PT_CUDA_CHECK(ctx, cudaEventRecord(ctx->ev_shadowed, st_sh)); shadow_pending = true; }
             }
         }
         iters += kItersPerBatch;
+        if (overlap && shadow_pending) { PT_CUDA_CHECK(ctx, cudaStreamWaitEvent(st, ctx->ev_shadowed, 0)); shadow_pending = false; }
         PT_CUDA_CHECK(ctx, cudaMemcpyAsync(ctx->h_counters, ctx->d_counters, 8 * C_TOTAL, cudaMemcpyDeviceToHost, st));
         PT_CUDA_CHECK(ctx, cudaStreamSynchronize(st));
         prof_collect();
