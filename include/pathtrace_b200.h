@@ -172,6 +172,15 @@ int32_t pt_trace_primary(pt_context* ctx, const pt_scene* scene, const pt_camera
 /* LBVH download: codes_sorted[n], prim_sorted[n], nodes[max(n-1,1)*16 words], bounds[6] = scene min.xyz, max.xyz. */
 int32_t pt_bvh_download(pt_context* ctx, const pt_scene* scene, uint32_t* codes_sorted, uint32_t* prim_sorted, uint32_t* nodes,
                         float* bounds);
+/* Host-only hook (needs no device): the pixel rectangles with which the camera rays' constant-bank scan is culled
+ * (csrc/pt_wave.cuh: make_cull_param, closest_hit_param_culled) for a scene of at most 8 triangle pairs.  Entries are in scan
+ * order — the pairs of consecutive triangles first, then the unpaired primitives.  rects: 4 int32 per entry = x0, y0, x1, y1
+ * (inclusive, y counted from the BOTTOM row like camera.rs:139-147 after the flip of world.rs:299; x0 > x1 = empty; the full
+ * screen when the entry cannot be bounded); entry_of_object: n_objects int32.  A camera ray of pixel (x, y) with offsets in
+ * [0, 1] can only hit objects whose entry's rectangle contains (x, y) — the property tests/test_host_and_abi.py checks against
+ * the oracle.  Returns PT_ERR_INVALID when the scene has no such scan (more than 8 pairs or more than 1024 objects). */
+int32_t pt_primary_cull_rects(const pt_shape* shapes, uint32_t n_objects, const pt_camera* cam, int32_t* rects, int32_t* entry_of_object,
+                              uint32_t* n_entries);
 uint32_t pt_scene_num_objects(const pt_scene* scene);
 uint32_t pt_scene_num_lights(const pt_scene* scene);
 /* Device time (CUDA events) of the LBVH build inside pt_scene_create — primitive boxes, Morton codes, radix sort, hierarchy,

@@ -61,7 +61,7 @@ EXPORTS = ["pt_context_create", "pt_context_destroy", "pt_last_error", "pt_scene
            "pt_trace_primary", "pt_bvh_download", "pt_scene_num_objects", "pt_scene_num_lights", "pt_scene_build_ms",
            "pt_scene_build_launches", "pt_export_luminance", "pt_write_ppm", "pt_version", "pt_measure_fp32_peak",
            "pt_group_create", "pt_group_destroy", "pt_group_size", "pt_group_context", "pt_group_last_error",
-           "pt_group_scene_create", "pt_group_scene_destroy", "pt_group_render", "pt_render_device_noalloc"]
+           "pt_group_scene_create", "pt_group_scene_destroy", "pt_group_render", "pt_render_device_noalloc", "pt_primary_cull_rects"]
 
 _lib = None
 
@@ -258,6 +258,20 @@ def render_device_noalloc(ctx: Context, scene: Scene, cam: Camera, params: pt_re
     c = camera_struct(cam)
     ctx.check(ctx.lib.pt_render_device_noalloc(ctx.handle, scene.handle, C.byref(c), C.byref(params), C.c_void_p(d_radiance_ptr or None),
                                                C.c_void_p(d_rgba_ptr or None)), "pt_render_device_noalloc")
+
+
+def primary_cull_rects(shapes: np.ndarray, cam: Camera):
+    """pt_primary_cull_rects (host only, no device): (rects[n_entries, 4] = x0, y0, x1, y1 inclusive with y from the bottom row,
+    entry_of_object[n])."""
+    lib = load_library()
+    shapes = np.ascontiguousarray(shapes, dtype=SHAPE_DTYPE)
+    n = shapes.shape[0]
+    rects = np.zeros((max(n, 1), 4), np.int32); ent = np.zeros(max(n, 1), np.int32); ne = C.c_uint32(0)
+    c = camera_struct(cam)
+    rc = lib.pt_primary_cull_rects(_ptr(shapes), C.c_uint32(n), C.byref(c), _ptr(rects), _ptr(ent), C.byref(ne))
+    if rc:
+        raise PathtraceError(f"pt_primary_cull_rects failed ({rc}): {lib.pt_last_error(None).decode()}")
+    return rects[:ne.value].copy(), ent[:n].copy()
 
 
 def trace_primary(ctx: Context, scene: Scene, cam: Camera, params: pt_render_params = None, jitter=False, ox=0.5, oy=0.5, sample=0,

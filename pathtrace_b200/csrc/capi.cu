@@ -411,6 +411,15 @@ int32_t pt_trace_primary(pt_context* ctx, const pt_scene* scene, const pt_camera
     return keep(ctx, rc);
 }
 
+int32_t pt_primary_cull_rects(const pt_shape* shapes, uint32_t n, const pt_camera* cam, int32_t* rects, int32_t* entry_of_object, uint32_t* n_entries) {
+    if (!shapes || !rects || !entry_of_object || !n_entries) return fail(nullptr, PT_ERR_INVALID, "pt_primary_cull_rects: null argument");
+    if (!valid_camera(cam)) return fail(nullptr, PT_ERR_INVALID, "pt_primary_cull_rects: bad camera (width/height must be >= 2)");
+    for (uint32_t i = 0; i < n; ++i) if (shapes[i].kind > PT_SHAPE_TRIANGLE) return fail(nullptr, PT_ERR_INVALID, "pt_primary_cull_rects: unknown shape kind");
+    if (!primary_cull_rects_host(shapes, n, *cam, rects, entry_of_object, n_entries))
+        return fail(nullptr, PT_ERR_INVALID, "pt_primary_cull_rects: the scene has no constant-bank scan (empty, more than 1024 objects or more than 8 triangle pairs)");
+    return PT_OK;
+}
+
 int32_t pt_bvh_download(pt_context* ctx, const pt_scene* scene, uint32_t* codes, uint32_t* prims, uint32_t* nodes, float* bounds) {
     if (!ctx || !scene) return fail(ctx, PT_ERR_INVALID, "pt_bvh_download: null argument");
     cudaSetDevice(ctx->device);

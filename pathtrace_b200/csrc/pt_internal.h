@@ -102,6 +102,8 @@ int smem_wavefront_render_noalloc(pt_context* ctx, const SceneDev& scene, const 
                                   float* d_radiance, uint8_t* d_rgba);
 int wavefront_trace_primary(pt_context* ctx, const SceneDev& scene, const pt_camera& cam, const pt_render_params& prm, int jitter,
                             float ox, float oy, uint32_t sample, int32_t* d_obj, float* d_t, float* d_dir, uint64_t* launches);
+// host only: the cull rectangles of make_cull_param in scan order (pt_primary_cull_rects); false when the scene has no constant-bank scan
+bool primary_cull_rects_host(const pt_shape* shapes, uint32_t n, const pt_camera& cam, int32_t* rects, int32_t* entry_of_object, uint32_t* n_entries);
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba);
 // total += batch; moment2 += batch^2 (per pixel and channel); batch is zeroed for the next one
 int fold_moments_launch(pt_context* ctx, float4* d_batch, float4* d_total, float4* d_moment2, uint32_t npix);

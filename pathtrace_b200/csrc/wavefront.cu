@@ -571,6 +571,41 @@ int fp32_peak_launch(pt_context* ctx, float* tflops, float* ms_out) {
     return PT_OK;
 }
 
+bool primary_cull_rects_host(const pt_shape* shapes, uint32_t n, const pt_camera& cam, int32_t* rects, int32_t* entry_of_object, uint32_t* n_entries) {
+    if (n == 0 || n > 1024) return false;
+    SceneDev sc;                                          // host fields only: what make_cull_param reads
+    sc.n_objects = n;
+    sc.shapes_host.assign(shapes, shapes + n);
+    uint32_t pairs = 0, entries = 0;
+    for (uint32_t i = 0; i < n; ++entries) {              // the pairing rule of pt_scene_create / k_brute_table
+        const bool pair = i + 1 < n && shapes[i].kind == PT_SHAPE_TRIANGLE && shapes[i + 1].kind == PT_SHAPE_TRIANGLE;
+        pairs += pair; i += pair ? 2 : 1;
+    }
+    if (pairs > (uint32_t)kParamPairs) return false;
+    sc.n_pairs = pairs; sc.n_brute = entries;
+    const CullParam cp = make_cull_param(sc, cam, true);
+    auto put = [&](uint32_t e, int4 r) {
+        const bool empty = r.x == 0x7fffffff;
+        const bool full = r.z == 0x7fffffff;
+        rects[4 * e] = empty ? 1 : r.x; rects[4 * e + 1] = empty ? 1 : r.y;
+        rects[4 * e + 2] = empty ? 0 : full ? (int32_t)cam.width - 1 : r.x + r.z; rects[4 * e + 3] = empty ? 0 : full ? (int32_t)cam.height - 1 : r.y + r.w;
+    };
+    uint32_t ep = 0, es = 0;
+    for (uint32_t i = 0; i < n;) {
+        const bool pair = i + 1 < n && shapes[i].kind == PT_SHAPE_TRIANGLE && shapes[i + 1].kind == PT_SHAPE_TRIANGLE;
+        if (pair) {
+            put(ep, cp.pair[(size_t)kParamPairs - pairs + ep]);
+            entry_of_object[i] = entry_of_object[i + 1] = (int32_t)ep; ++ep; i += 2;
+        } else {
+            const uint32_t e = pairs + es;
+            put(e, es < (uint32_t)kCullSingles ? cp.single[es] : make_int4(0, 0, 0x7fffffff, 0x7fffffff));
+            entry_of_object[i] = (int32_t)e; ++es; i += 1;
+        }
+    }
+    *n_entries = entries;
+    return true;
+}
+
 int resolve_launch(pt_context* ctx, const float4* d_accum, uint32_t w, uint32_t h, uint32_t spp, float* d_rad, uint8_t* d_rgba) {
     uint32_t npix = w * h;
     k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(d_accum, npix, (float)spp, d_rad, reinterpret_cast<uchar4*>(d_rgba));

@@ -152,6 +152,8 @@ extern "C" {
 
     pub fn pt_trace_primary(ctx: *mut pt_context, scene: *const pt_scene, cam: *const pt_camera, p: *const pt_render_params,
                             jitter: i32, ox: f32, oy: f32, sample: u32, obj_id: *mut i32, t: *mut f32, dir_or_null: *mut f32) -> i32;
+    pub fn pt_primary_cull_rects(shapes: *const pt_shape, n_objects: u32, cam: *const pt_camera, rects: *mut i32, entry_of_object: *mut i32,
+                                 n_entries: *mut u32) -> i32;
     pub fn pt_bvh_download(ctx: *mut pt_context, scene: *const pt_scene, codes_sorted: *mut u32, prim_sorted: *mut u32,
                            nodes: *mut u32, bounds: *mut f32) -> i32;
 
