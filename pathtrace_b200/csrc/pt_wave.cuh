@@ -39,6 +39,7 @@ struct SceneView {
     uint32_t n_objects, n_lights, n_nodes;
     const float4* brute;     // brute-force scan table (may be null)
     uint32_t n_brute, n_pairs;
+    float box_pad, ro_near;  // one-FMA box test from shared memory (slab_fma): boxes are padded by box_pad when staged, which covers ray origins with |ro| <= ro_near
 };
 
 // n / d for any 32-bit n with the host's m = floor(2^64 / d) + 1 (d >= 2): exact, because n * (m * d - 2^64) < 2^64.
@@ -81,6 +82,7 @@ struct Geo {
     const float4* brute = nullptr;   // smem copy of the brute-force scan table, n_brute entries of 5 float4 (null: scan prims):
     uint32_t n_brute = 0, n_pairs = 0;   // n_pairs triangle pairs first, then the unpaired primitives
     const float4* prims;   // stride PS (smem: 3 = q0,q1,q2 only; 4 = with the normal) or 4 (global)
+    float ro_near = 0.f;   // see SceneView
     PT_DEV void node(int i, float4& a, float4& b, float4& c, float4& d) const {
         if (SMEM) { a = nodes[4 * i]; b = nodes[4 * i + 1]; c = nodes[4 * i + 2]; d = nodes[4 * i + 3]; }
         else { a = __ldg(nodes + 4 * i); b = __ldg(nodes + 4 * i + 1); c = __ldg(nodes + 4 * i + 2); d = __ldg(nodes + 4 * i + 3); }
@@ -101,10 +103,15 @@ PT_DEV Geo<SMEM> stage_scene(const SceneView& s, float4* smem, bool want_nodes) 
             return g;
         }
         uint32_t nn = want_nodes ? s.n_nodes * 4 : 0;
-        for (uint32_t i = threadIdx.x; i < nn; i += blockDim.x) smem[i] = __ldg(s.nodes + i);
+        for (uint32_t i = threadIdx.x; i < nn; i += blockDim.x) {       // [Llo,left][Lhi,right][Rlo,0][Rhi,0]: boxes padded outward by box_pad
+            float4 v = __ldg(s.nodes + i);
+            const float p = (i & 1u) ? s.box_pad : -s.box_pad;
+            v.x += p; v.y += p; v.z += p;
+            smem[i] = v;
+        }
         for (uint32_t i = threadIdx.x; i < s.n_objects * 3; i += blockDim.x) smem[nn + i] = __ldg(s.prims + 4 * (i / 3) + (i % 3));
         __syncthreads();
-        g.nodes = smem; g.prims = smem + nn;
+        g.nodes = smem; g.prims = smem + nn; g.ro_near = s.ro_near;
     } else {
         g.nodes = s.nodes; g.prims = s.prims;
     }
@@ -122,11 +129,14 @@ PT_DEV bool slab(float3 lo, float3 hi, float3 ro, float3 inv, float t_min, float
     return tn <= tf * 1.0000004f;
 }
 
-// The same test with one FMA per plane: t = lo * inv + c, c = -(ro * inv) rounded once per ray.  Against the form above each
-// plane distance carries an extra absolute error of at most u |c| (u = 2^-24: the rounding of c), so the caller passes
-// slack >= 2 * 1.5 u max|c| and the comparison becomes tn <= tf (1 + 4e-7) + slack: still conservative, i.e. a superset of
-// the boxes the exact-form test enters, so ids and t of the walk are unchanged.  (A zero direction component makes c and the
-// slack infinite: such a ray enters every box — correct, and of measure zero.)
+// The same test with one FMA per plane: t = lo * inv + c, c = -(ro * inv) rounded once per ray.  Against the form above the
+// plane distances of axis k carry an extra absolute error of u |c_k| (u = 2^-24: the rounding of c), i.e. the planes of that
+// axis are displaced by at most u |ro_k| in space.  The boxes staged in shared memory are padded by box_pad = 8 u max|scene
+// coordinate| (stage_scene), which covers every origin with |ro_k| <= ro_near = 4 max|scene coordinate| whatever the direction;
+// a ray that starts farther away (a distant camera) gets slack = 3 u max|c| added to the comparison instead.  Either way the
+// test enters a superset of the boxes the exact form enters, so ids and t of the walk are unchanged.  (A slack for every ray
+// was the first form: a near-axis-parallel ray has |c_k| ~ 1e6, lost all culling and walked the whole tree — a handful of
+// such rays per launch set its duration on large trees.)
 PT_DEV bool slab_fma(float3 lo, float3 hi, float3 inv, float3 c, float t_min, float t_max, float slack, float& tnear) {
     float tx0 = fmaf(lo.x, inv.x, c.x), tx1 = fmaf(hi.x, inv.x, c.x);
     float ty0 = fmaf(lo.y, inv.y, c.y), ty1 = fmaf(hi.y, inv.y, c.y);
@@ -136,9 +146,10 @@ PT_DEV bool slab_fma(float3 lo, float3 hi, float3 inv, float3 c, float t_min, fl
     tnear = tn;
     return tn <= fmaf(tf, 1.0000004f, slack);
 }
-PT_DEV void slab_fma_setup(float3 ro, float3 inv, float3& c, float& slack) {
+PT_DEV void slab_fma_setup(float3 ro, float3 inv, float ro_near, float3& c, float& slack) {
     c = v3(-(ro.x * inv.x), -(ro.y * inv.y), -(ro.z * inv.z));
-    slack = 1.8e-7f * fmaxf(fmaxf(fabsf(c.x), fabsf(c.y)), fabsf(c.z));    // 3 u max|c| = 1.79e-7 max|c|
+    const bool near = fmaxf(fmaxf(fabsf(ro.x), fabsf(ro.y)), fabsf(ro.z)) <= ro_near;
+    slack = near ? 0.0f : 1.8e-7f * fmaxf(fmaxf(fabsf(c.x), fabsf(c.y)), fabsf(c.z));    // 3 u max|c| = 1.79e-7 max|c|
 }
 
 // ---- brute-force scan table (lbvh.cu: k_brute_table): triangle pairs in ascending object order, then the unpaired primitives.
@@ -476,7 +487,7 @@ PT_DEV void bvh_stream(const G& g, float t_min, Next next, Finish finish, unsign
             if (next(node == kWalkDone, idle, o, d, tm, sl, exhausted)) {
                 ro = o; rd = d; tmax = tm; slot = sl; best_id = -1; sp = 0; node = 0;
                 inv = v3(__frcp_rn(d.x), __frcp_rn(d.y), __frcp_rn(d.z));   // exact: the slab margins assume IEEE reciprocals
-                if (SMEM) slab_fma_setup(o, inv, cneg, slack);
+                if (SMEM) slab_fma_setup(o, inv, g.ro_near, cneg, slack);
             }
         }
         // inner nodes: descend until this lane holds a leaf (negative: ~object id) or its stack runs empty.  The warp leaves
@@ -689,6 +700,9 @@ inline SceneView make_scene_view(const SceneDev& d) {
     v.prims = d.prims; v.mats = d.mats; v.light_ids = d.light_ids; v.nodes = d.nodes;
     v.n_objects = d.n_objects; v.n_lights = d.n_lights; v.n_nodes = d.n_nodes;
     v.brute = d.brute; v.n_brute = d.n_brute; v.n_pairs = d.n_pairs;
+    float mx = 0.f;
+    for (int k = 0; k < 6; ++k) if (std::isfinite(d.bounds[k]) && std::fabs(d.bounds[k]) < 1e30f) mx = std::fmax(mx, std::fabs(d.bounds[k]));
+    v.box_pad = 8.0f * 5.9604645e-8f * mx; v.ro_near = 4.0f * mx;
     return v;
 }
 // Which form of the brute-force scan a scene / camera / PT_TRAVERSAL_* value gets (pt_stats.scan_mode): 1 = scan table from
