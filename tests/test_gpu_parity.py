@@ -283,3 +283,31 @@ def test_primary_cull_is_exact_for_any_camera(cam_name, scene_name, oracle, gpu_
         assert n_hit > 0
     else:
         assert n_hit == 0
+
+
+@pytest.mark.parametrize("pose", ["far", "axis_aligned"])
+def test_bvh_stream_walk_is_exact_for_far_and_axis_parallel_rays(pose, gpu_ctx):
+    """The shared-memory walk tests boxes with one FMA per plane (pt_wave.cuh: slab_fma): exact for ray origins within four
+    scene radii thanks to the padded boxes, and through a slack on the comparison beyond.  A camera 300 scene radii away
+    (telephoto) takes the second branch for every primary ray; a camera looking straight down an axis produces rays with
+    zero direction components (infinite reciprocals).  Same paths as the brute-force scan in both cases."""
+    from pathtrace_b200 import api
+    from pathtrace_b200.objects import Camera, Vector3 as V
+    sh, mt, _ = _scenes()["random300"]
+    if pose == "far":
+        cam = Camera.look_at(V.new(300.0, 200.0, 900.0), V.new(0, 0, -2.5), V.new(0, 1, 0), 96, 64, 0.2)
+    else:
+        cam = Camera.new(V.new(0, 0, 2), 97, 65, 1.0, 35.0)          # odd frame: the centre column / row look exactly along -z
+    sc = api.Scene(gpu_ctx, sh, mt)
+    out = {}
+    for trav in ("bvh", "brute"):
+        out[trav] = api.render(gpu_ctx, sc, cam, api.render_params(spp=16, hbm_queues=True, traversal=trav))
+    ids, t, _ = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal="bvh"))
+    ids2, t2, _ = api.trace_primary(gpu_ctx, sc, cam, api.render_params(traversal="brute"))
+    sc.close()
+    assert np.array_equal(ids, ids2) and np.array_equal(t.view(np.uint32), t2.view(np.uint32))
+    assert (ids >= 0).sum() > 50
+    (ra, _, sa), (rb, _, sb) = out["bvh"], out["brute"]
+    for k in ("samples", "rays_primary", "rays_shadow", "rays_scattered", "path_vertices"):
+        assert sa[k] == sb[k], (k, sa[k], sb[k])
+    assert np.abs(ra - rb).max() <= 2e-4 * max(float(np.abs(rb).max()), 1.0)
